@@ -1,0 +1,136 @@
+/* b200vec.h — C-ABI of the B200-native vector-build engine (libb200vec.so).
+ *
+ * Drop-in boundary for ONE hot path of ramiyako/vector: the composite I/Q vector build
+ * (generate_vector in unified_gui.py / main.py) and the utils.py helpers it leans on.
+ * The reference has no native interface; its boundary is a set of Python names.  Each
+ * entry point below says which reference lines it replaces (paths relative to the
+ * reference root).  INTEGRATION.md shows the ctypes binding a maintainer adds.
+ *
+ * Conventions
+ *   - plain C types only; every pointer called *_dev is a CUDA device pointer on the
+ *     context's device, every other pointer is host memory;
+ *   - complex64 is interleaved float32 (re, im), 8 bytes per sample — numpy's layout;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); all
+ *     calls are asynchronous on it unless stated otherwise;
+ *   - every function returns 0 on success, non-zero on error and never throws;
+ *     b200vec_last_error() gives a thread-local message for the last failure;
+ *   - the caller owns every buffer it passes; the library owns only its context
+ *     (packet bank, twiddle/window tables, select/FFT scratch) and allocates nothing
+ *     inside build/stft/db/select/quantize calls once scratch is warm.
+ *   - there is NO CPU fallback: without a CUDA device b200vec_create fails.
+ */
+#ifndef B200VEC_H
+#define B200VEC_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200VEC_ABI_VERSION 1
+#define B200VEC_MAX_PACKETS 32      /* descriptors per build call (reference: MAX_PACKETS = 6, unified_gui.py:41) */
+#define B200VEC_MAX_SLOTS   64      /* packet-bank slots per context */
+#define B200VEC_MAX_RANKS   8       /* order statistics per select call */
+
+typedef struct b200vec_ctx b200vec_ctx;
+
+/* One packet's placement, all integers computed on the host exactly as the reference does
+ * (unified_gui.py:1748-1757, main.py:247-253): instance k sits at start + k*period for
+ * 0 <= k < count, and `count` is the number of instances that fit entirely. */
+typedef struct b200vec_pkt_desc {
+    int64_t start;     /* first instance, vector-absolute sample index, >= 0 */
+    int64_t period;    /* > 0 */
+    int64_t count;     /* K_p, may be 0 */
+    int32_t slot;      /* bank slot holding the committed (resampled/shifted) packet */
+    int32_t reserved;
+} b200vec_pkt_desc;
+
+enum b200vec_build_mode {
+    B200VEC_BUILD_STORE   = 0,  /* place and store, no normalisation (normalize unchecked) */
+    B200VEC_BUILD_MAXONLY = 1,  /* pass A: place in registers, reduce max |v|^2, store nothing */
+    B200VEC_BUILD_SCALE   = 2   /* pass B: place, multiply by 1/sqrt(*maxsq_dev), store */
+};
+
+int         b200vec_abi_version(void);
+const char *b200vec_last_error(void);
+
+/* Lifetime.  `device` is a CUDA ordinal. */
+int b200vec_create(int device, b200vec_ctx **out);
+int b200vec_destroy(b200vec_ctx *ctx);
+
+/* ---- packet bank -------------------------------------------------------------------
+ * upload   : what load_packet_info returns (utils.py:89-105), complex64 [len].
+ * resample : scipy.signal.resample(signal, len_out) as called at utils.py:117
+ *            (Fourier method: forward DFT, copy the min(len,len_out) lowest-|f| bins,
+ *            split/unite the unpaired Nyquist bin, inverse DFT); computed in fp64 on the
+ *            device (Bluestein over power-of-two FFTs), rounded once to complex64.
+ * shift    : apply_frequency_shift (utils.py:120-127): y[n] *= exp(j*(2*pi*f)*(n/fs)),
+ *            phase in fp64 from the integer packet-local index, one rounding to complex64.
+ *            freq_hz == 0 commits the samples unchanged (utils.py:122-123).
+ *            shift also "commits" the slot: it writes the two 16-byte-phase copies the
+ *            placement kernel reads.  A slot must be committed before b200vec_build.
+ * download : committed samples back to the host (synchronises the stream). */
+int b200vec_bank_upload(b200vec_ctx *ctx, int slot, const void *src, int64_t len,
+                        int src_is_device, void *stream);
+int b200vec_bank_resample(b200vec_ctx *ctx, int slot, int64_t len_out, void *stream);
+int b200vec_bank_shift(b200vec_ctx *ctx, int slot, double freq_hz, double fs_hz, void *stream);
+int b200vec_bank_len(b200vec_ctx *ctx, int slot, int64_t *len_out);
+int b200vec_bank_download(b200vec_ctx *ctx, int slot, void *dst_host, int64_t len, void *stream);
+
+/* ---- vector build ------------------------------------------------------------------
+ * Replaces np.zeros + the placement loop + normalisation:
+ *   unified_gui.py:1712, 1757-1769, 1778-1782;  main.py:218, 253-257, 274-277.
+ * Computes output samples [slab_lo, slab_hi) of the vector into out_dev[0 .. slab_hi-slab_lo)
+ * (complex64, 16-byte aligned).  Every sample of the slab is written exactly once
+ * (zeros included); contributions are summed in (packet, instance) order like the
+ * reference's in-place adds.  maxsq_dev points at ONE device double holding max |v|^2:
+ *   MAXONLY atomically raises it (caller zeroes it first; a multi-GPU caller all-reduces
+ *   it with MAX between the passes), SCALE reads it and multiplies every sample by
+ *   fl32(1 / fl32(sqrt(maxsq))) when maxsq > 0 — numpy's complex64 / float32-scalar. */
+int b200vec_build(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                  int64_t slab_lo, int64_t slab_hi, void *out_dev, int mode,
+                  double *maxsq_dev, void *stream);
+
+/* ---- spectrogram -------------------------------------------------------------------
+ * scipy.signal.spectrogram(x[::stride], window, nperseg, noverlap=nperseg-hop, nfft,
+ * return_onesided=False, detrend=False, scaling) followed by fftshift(axes=0), as called at
+ * utils.py:281-291/303-313/324-347/350-351 and vector_analyzer/spectrogram_analysis.py:40-53.
+ * Frame f (global index) reads decimated samples f*hop .. f*hop+nperseg-1, i.e. vector
+ * samples (f*hop+j)*stride; in_dev[0] is vector sample `in_origin`.  Frames
+ * [frame_lo, frame_lo+n_frames) are written to out_dev[row*out_ld + (f-frame_lo)], row r
+ * holding bin (r + nfft/2) mod nfft (the fftshift); float32 PSD = |X|^2 * scale.
+ * *nonzero_flag_dev (int, optional) is OR-ed with 1 if any output > 0 (utils.py:316).
+ * window_dev: nperseg float32 taps on the device (the host builds them the way
+ * scipy.signal.get_window does and casts to float32, as _spectral_helper does).
+ * nfft must be a power of two in [32, 16384]; nperseg <= nfft. */
+int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_t in_len,
+                 int64_t stride, int nperseg, int hop, int nfft, const float *window_dev, float scale,
+                 int64_t frame_lo, int64_t n_frames, float *out_dev, int64_t out_ld,
+                 int *nonzero_flag_dev, void *stream);
+
+/* ---- dB map and order statistics (normalize_spectrogram, utils.py:356-404) -----------
+ * db      : out[i] = 10*log10(|s[i]| + floor)                      (utils.py:363-368)
+ * select  : exact order statistics of a float32 array: ranks[] are 0-based positions in the
+ *           ascending sort of the selected elements (all, or only those > 0 when
+ *           positive_only — utils.py:365 takes the percentile of Sxx_abs[Sxx_abs > 0]).
+ *           count_host receives how many elements were selected.  Two-call protocol so the
+ *           host can derive ranks from the count the way np.percentile does:
+ *           select_count() then select_ranks().  Both synchronise the stream. */
+int b200vec_db(b200vec_ctx *ctx, const float *s_dev, int64_t n, float floor_val,
+               float *out_dev, void *stream);
+int b200vec_select_count(b200vec_ctx *ctx, const float *data_dev, int64_t n, int positive_only,
+                         int64_t *count_host, void *stream);
+int b200vec_select_ranks(b200vec_ctx *ctx, const float *data_dev, int64_t n, int positive_only,
+                         const int64_t *ranks_host, int n_ranks, float *values_host,
+                         void *stream);
+
+/* ---- .wv payload (mat2wv, vector_analyzer/mat_to_wv_converter.py:42-50) ---------------
+ * out[2i] = (int16) trunc(re*32767), out[2i+1] = (int16) trunc(im*32767). */
+int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, int16_t *out_dev,
+                        void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200VEC_H */

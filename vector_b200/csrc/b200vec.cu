@@ -1,0 +1,324 @@
+// b200vec.cu — C-ABI of libb200vec.so (see include/b200vec.h for the contract and the
+// reference lines each entry point replaces).  sm_100a only; no CPU fallback.
+#include "common.cuh"
+#include "bank.cuh"
+#include "place.cuh"
+#include "stft.cuh"
+#include "stft1024.cuh"
+#include "select.cuh"
+
+namespace b200vec {
+thread_local std::string g_last_error;
+
+// K6: mat2wv quantiser (vector_analyzer/mat_to_wv_converter.py:42-50): x*32767 in float32,
+// truncation toward zero, int16 I/Q interleave.  Out-of-range values wrap modulo 2^16 like
+// the x86 cvttss2si + narrowing the reference's astype(int16) compiles to.
+__global__ void __launch_bounds__(256)
+wv_quantize_kernel(const float2 *__restrict__ in, long long n, short2 *__restrict__ out) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float2 v = __ldg(in + i);
+        const int re = __float2int_rz(v.x * 32767.0f);
+        const int im = __float2int_rz(v.y * 32767.0f);
+        out[i] = make_short2((short)re, (short)im);
+    }
+}
+
+__global__ void sel_init(unsigned int *hist, SelState init) {
+    *reinterpret_cast<SelState *>(hist + kStateOff) = init;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+static int run_select(b200vec_ctx *ctx, const float *data, long long n, int positive_only,
+                      const int64_t *ranks, int nr, cudaStream_t st, SelState *host_state) {
+    B2_CUDA(cudaMemsetAsync(ctx->hist, 0, sizeof(unsigned int) * kHistWords, st));
+    SelState init;
+    memset(&init, 0, sizeof(init));
+    init.n_ranks = nr;
+    for (int r = 0; r < nr; ++r) init.resid[r] = (unsigned long long)ranks[r];
+    sel_init<<<1, 1, 0, st>>>(ctx->hist, init);
+    const unsigned grid = (unsigned)(ctx->sm_count * 8);
+    if (n > 0) sel_hist1<<<grid, kSelThreads, 0, st>>>(data, n, positive_only, ctx->hist);
+    sel_pick<1><<<1, 1, 0, st>>>(ctx->hist);
+    if (nr > 0 && n > 0) {
+        sel_histN<2><<<grid, kSelThreads, (size_t)nr * kBins2 * 4, st>>>(data, n, positive_only, ctx->hist);
+        sel_pick<2><<<1, 1, 0, st>>>(ctx->hist);
+        sel_histN<3><<<grid, kSelThreads, (size_t)nr * kBins3 * 4, st>>>(data, n, positive_only, ctx->hist);
+        sel_pick<3><<<1, 1, 0, st>>>(ctx->hist);
+    }
+    B2_CUDA(cudaGetLastError());
+    B2_CUDA(cudaMemcpyAsync(ctx->pinned, ctx->hist + kStateOff, sizeof(SelState),
+                            cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    memcpy(host_state, ctx->pinned, sizeof(SelState));
+    return 0;
+}
+
+}  // namespace b200vec
+
+using namespace b200vec;
+
+extern "C" {
+
+int b200vec_abi_version(void) { return B200VEC_ABI_VERSION; }
+
+const char *b200vec_last_error(void) { return g_last_error.c_str(); }
+
+int b200vec_create(int device, b200vec_ctx **out) {
+    B2_REQUIRE(out != nullptr, "out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail("b200vec_create", "no CUDA device available (this library has no CPU fallback)");
+    B2_REQUIRE(device >= 0 && device < count, "device ordinal out of range");
+    DeviceGuard g(device);
+    cudaDeviceProp prop;
+    B2_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail("b200vec_create", "kernels are built for sm_100a only (need a Blackwell B200-class GPU)");
+    b200vec_ctx *ctx = new b200vec_ctx();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    B2_CUDA(cudaMalloc(&ctx->hist, sizeof(unsigned int) * kHistWords));
+    B2_CUDA(cudaMallocHost(&ctx->pinned, 4096));
+    B2_CUDA(cudaFuncSetAttribute(sel_histN<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 B200VEC_MAX_RANKS * kBins2 * 4));
+    B2_CUDA(cudaFuncSetAttribute(sel_histN<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 B200VEC_MAX_RANKS * kBins3 * 4));
+    B2_CUDA(cudaFuncSetAttribute(stft_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 200 * 1024));
+    if (stft1024_setup()) { delete ctx; return 1; }
+    *out = ctx;
+    return 0;
+}
+
+int b200vec_destroy(b200vec_ctx *ctx) {
+    if (!ctx) return 0;
+    DeviceGuard g(ctx->device);
+    cudaDeviceSynchronize();
+    for (auto &s : ctx->slots) {
+        if (s.raw) cudaFree(s.raw);
+        if (s.store) cudaFree(s.store);
+    }
+    for (auto &kv : ctx->twiddles) cudaFree(kv.second);
+    for (auto &s : ctx->fft64) if (s.ptr) cudaFree(s.ptr);
+    if (ctx->hist) cudaFree(ctx->hist);
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    delete ctx;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+int b200vec_bank_upload(b200vec_ctx *ctx, int slot, const void *src, int64_t len,
+                        int src_is_device, void *stream) {
+    B2_REQUIRE(ctx, "ctx is NULL");
+    B2_REQUIRE(slot >= 0 && slot < B200VEC_MAX_SLOTS, "slot out of range");
+    B2_REQUIRE(len > 0 && len < (1LL << 31) - 2 * kTile, "packet length must be in (0, 2^31)");
+    B2_REQUIRE(src, "src is NULL");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    BankSlot &sl = ctx->slots[slot];
+    if (sl.cap_raw < len) {
+        B2_CUDA(cudaStreamSynchronize(st));
+        if (sl.raw) cudaFree(sl.raw);
+        sl.raw = nullptr; sl.cap_raw = 0;
+        B2_CUDA(cudaMalloc(&sl.raw, (size_t)len * sizeof(float2)));
+        sl.cap_raw = len;
+    }
+    B2_CUDA(cudaMemcpyAsync(sl.raw, src, (size_t)len * sizeof(float2),
+                            src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    sl.len_raw = len;
+    sl.len = 0;
+    return 0;
+}
+
+int b200vec_bank_resample(b200vec_ctx *ctx, int slot, int64_t len_out, void *stream) {
+    B2_REQUIRE(ctx, "ctx is NULL");
+    B2_REQUIRE(slot >= 0 && slot < B200VEC_MAX_SLOTS, "slot out of range");
+    BankSlot &sl = ctx->slots[slot];
+    B2_REQUIRE(sl.len_raw > 0, "slot is empty");
+    B2_REQUIRE(len_out > 0, "scipy.signal.resample needs num > 0");
+    DeviceGuard g(ctx->device);
+    return resample_slot(ctx, sl, len_out, (cudaStream_t)stream);
+}
+
+int b200vec_bank_shift(b200vec_ctx *ctx, int slot, double freq_hz, double fs_hz, void *stream) {
+    B2_REQUIRE(ctx, "ctx is NULL");
+    B2_REQUIRE(slot >= 0 && slot < B200VEC_MAX_SLOTS, "slot out of range");
+    BankSlot &sl = ctx->slots[slot];
+    B2_REQUIRE(sl.len_raw > 0, "slot is empty");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t len = sl.len_raw;
+    if (sl.cap_store < len) {
+        B2_CUDA(cudaStreamSynchronize(st));
+        if (sl.store) cudaFree(sl.store);
+        sl.store = nullptr; sl.cap_store = 0;
+        // per copy: pad | samples (rounded up to even) | pad (+1 spare for the 8-byte phase of copy B)
+        const int64_t per = ((len + 1) & ~1LL) + 2 * kBankPad + 2;
+        B2_CUDA(cudaMalloc(&sl.store, (size_t)(2 * per) * sizeof(float2)));
+        sl.cap_store = len;
+    }
+    const int64_t per = ((sl.cap_store + 1) & ~1LL) + 2 * kBankPad + 2;
+    B2_CUDA(cudaMemsetAsync(sl.store, 0, (size_t)(2 * per) * sizeof(float2), st));
+    sl.a = sl.store + kBankPad;                 // cudaMalloc is 256-byte aligned, kBankPad is even -> 16-byte aligned
+    sl.b = sl.store + per + kBankPad + 1;       // per is even -> 8 mod 16
+    // the reference forms the phase as ((2j*pi)*f)*t: w = fl(fl(2*pi)*f)   (utils.py:126)
+    const double w = (2.0 * M_PI) * freq_hz;
+    shift_commit_kernel<<<(unsigned)((len + 255) / 256), 256, 0, st>>>(
+        sl.raw, len, w, fs_hz, freq_hz != 0.0 ? 1 : 0, sl.a, sl.b);
+    B2_CUDA(cudaGetLastError());
+    sl.len = len;
+    return 0;
+}
+
+int b200vec_bank_len(b200vec_ctx *ctx, int slot, int64_t *len_out) {
+    B2_REQUIRE(ctx && len_out, "NULL argument");
+    B2_REQUIRE(slot >= 0 && slot < B200VEC_MAX_SLOTS, "slot out of range");
+    *len_out = ctx->slots[slot].len ? ctx->slots[slot].len : ctx->slots[slot].len_raw;
+    return 0;
+}
+
+int b200vec_bank_download(b200vec_ctx *ctx, int slot, void *dst_host, int64_t len, void *stream) {
+    B2_REQUIRE(ctx && dst_host, "NULL argument");
+    B2_REQUIRE(slot >= 0 && slot < B200VEC_MAX_SLOTS, "slot out of range");
+    BankSlot &sl = ctx->slots[slot];
+    B2_REQUIRE(sl.len > 0, "slot is not committed (call b200vec_bank_shift first)");
+    B2_REQUIRE(len == sl.len, "length mismatch");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    B2_CUDA(cudaMemcpyAsync(dst_host, sl.a, (size_t)len * sizeof(float2), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+int b200vec_build(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                  int64_t slab_lo, int64_t slab_hi, void *out_dev, int mode,
+                  double *maxsq_dev, void *stream) {
+    B2_REQUIRE(ctx, "ctx is NULL");
+    B2_REQUIRE(n_pkts >= 0 && n_pkts <= B200VEC_MAX_PACKETS, "too many packets");
+    B2_REQUIRE(n_pkts == 0 || descs, "descs is NULL");
+    B2_REQUIRE(slab_lo >= 0 && slab_hi >= slab_lo, "bad slab");
+    B2_REQUIRE(mode == B200VEC_BUILD_MAXONLY || out_dev, "out_dev is NULL");
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || maxsq_dev, "maxsq_dev is NULL");
+    B2_REQUIRE(((uintptr_t)out_dev & 15) == 0, "out_dev must be 16-byte aligned");
+    PlaceArgs args;
+    memset(&args, 0, sizeof(args));
+    args.lo = slab_lo; args.hi = slab_hi;
+    int np = 0;
+    for (int i = 0; i < n_pkts; ++i) {
+        const b200vec_pkt_desc &d = descs[i];
+        B2_REQUIRE(d.slot >= 0 && d.slot < B200VEC_MAX_SLOTS, "descriptor slot out of range");
+        const BankSlot &sl = ctx->slots[d.slot];
+        B2_REQUIRE(sl.len > 0, "descriptor names an uncommitted bank slot");
+        B2_REQUIRE(d.period > 0, "period must be positive");
+        B2_REQUIRE(d.start >= 0 && d.count >= 0, "negative start/count");
+        if (d.count == 0) continue;
+        PlaceDesc &p = args.d[np++];
+        p.start = d.start; p.period = d.period; p.count = d.count;
+        p.len = (int)sl.len; p.a = sl.a; p.b = sl.b;
+    }
+    args.np = np;
+    DeviceGuard g(ctx->device);
+    return launch_place(ctx, args, (float2 *)out_dev, maxsq_dev, mode, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------
+int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_t in_len,
+                 int64_t stride, int nperseg, int hop, int nfft, const float *window_dev,
+                 float scale, int64_t frame_lo, int64_t n_frames, float *out_dev,
+                 int64_t out_ld, int *nonzero_flag_dev, void *stream) {
+    B2_REQUIRE(ctx && in_dev && out_dev && window_dev, "NULL argument");
+    B2_REQUIRE(nfft >= 32 && nfft <= 16384 && (nfft & (nfft - 1)) == 0,
+               "nfft must be a power of two in [32, 16384]");
+    B2_REQUIRE(nperseg >= 1 && nperseg <= nfft, "nfft must be greater than or equal to nperseg.");
+    B2_REQUIRE(hop >= 1, "noverlap must be less than nperseg.");
+    B2_REQUIRE(stride >= 1 && in_len >= 0 && n_frames >= 0 && out_ld >= n_frames, "bad geometry");
+    if (n_frames == 0) return 0;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nfft == 1024 && stft1024_enabled()) {
+        return launch_stft1024(ctx, (const float2 *)in_dev, in_origin, in_len, stride, nperseg, hop,
+                               window_dev, scale, frame_lo, n_frames, out_dev, out_ld,
+                               nonzero_flag_dev, st);
+    }
+    StftArgs a;
+    a.in = (const float2 *)in_dev; a.in_origin = in_origin; a.in_len = in_len; a.stride = stride;
+    a.nperseg = nperseg; a.hop = hop; a.nfft = nfft; a.log2n = ceil_log2(nfft);
+    a.window = window_dev; a.scale = scale; a.frame_lo = frame_lo; a.n_frames = n_frames;
+    a.out = out_dev; a.out_ld = out_ld; a.flag = nonzero_flag_dev;
+    a.T = stft_pick_T(nfft);
+    if (get_twiddles(ctx, nfft, &a.tw)) return 1;
+    const size_t smem = (size_t)nfft * 8 + (a.T > 1 ? (size_t)nfft * 4 * (a.T + 1) : 0);
+    const long long grid = (n_frames + a.T - 1) / a.T;
+    B2_REQUIRE(grid < (1LL << 31), "too many frames for one launch");
+    stft_generic_kernel<<<(unsigned)grid, kStftThreads, smem, st>>>(a);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+int b200vec_db(b200vec_ctx *ctx, const float *s_dev, int64_t n, float floor_val,
+               float *out_dev, void *stream) {
+    B2_REQUIRE(ctx && (n == 0 || (s_dev && out_dev)), "NULL argument");
+    if (n == 0) return 0;
+    DeviceGuard g(ctx->device);
+    long long grid = (n + kSelThreads - 1) / kSelThreads;
+    const long long cap = (long long)ctx->sm_count * 16;
+    if (grid > cap) grid = cap;
+    db_kernel<<<(unsigned)grid, kSelThreads, 0, (cudaStream_t)stream>>>(s_dev, n, floor_val, out_dev);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int b200vec_select_count(b200vec_ctx *ctx, const float *data_dev, int64_t n, int positive_only,
+                         int64_t *count_host, void *stream) {
+    B2_REQUIRE(ctx && count_host && (n == 0 || data_dev), "NULL argument");
+    DeviceGuard g(ctx->device);
+    SelState s;
+    if (run_select(ctx, data_dev, n, positive_only, nullptr, 0, (cudaStream_t)stream, &s)) return 1;
+    *count_host = (int64_t)s.count;
+    return 0;
+}
+
+int b200vec_select_ranks(b200vec_ctx *ctx, const float *data_dev, int64_t n, int positive_only,
+                         const int64_t *ranks_host, int n_ranks, float *values_host,
+                         void *stream) {
+    B2_REQUIRE(ctx && data_dev && ranks_host && values_host, "NULL argument");
+    B2_REQUIRE(n_ranks >= 1 && n_ranks <= B200VEC_MAX_RANKS, "n_ranks out of range");
+    B2_REQUIRE(n > 0, "empty input");
+    DeviceGuard g(ctx->device);
+    SelState s;
+    if (run_select(ctx, data_dev, n, positive_only, ranks_host, n_ranks, (cudaStream_t)stream, &s))
+        return 1;
+    for (int r = 0; r < n_ranks; ++r) {
+        B2_REQUIRE(ranks_host[r] >= 0 && (unsigned long long)ranks_host[r] < s.count,
+                   "rank outside the selected element count");
+        values_host[r] = key2f(s.result[r]);
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, int16_t *out_dev,
+                        void *stream) {
+    B2_REQUIRE(ctx && (n == 0 || (in_dev && out_dev)), "NULL argument");
+    if (n == 0) return 0;
+    DeviceGuard g(ctx->device);
+    long long grid = (n + 255) / 256;
+    const long long cap = (long long)ctx->sm_count * 16;
+    if (grid > cap) grid = cap;
+    wv_quantize_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(
+        (const float2 *)in_dev, n, (short2 *)out_dev);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

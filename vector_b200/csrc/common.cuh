@@ -1,0 +1,69 @@
+// common.cuh — shared declarations for libb200vec (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include <map>
+
+#include "../../include/b200vec.h"
+
+namespace b200vec {
+
+constexpr int kSmCount = 148;          // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+extern thread_local std::string g_last_error;
+
+inline int fail(const char *where, const char *msg) {
+    g_last_error = std::string(where) + ": " + msg;
+    return 1;
+}
+
+#define B2_CUDA(call)                                                                   \
+    do {                                                                                \
+        cudaError_t e__ = (call);                                                       \
+        if (e__ != cudaSuccess) {                                                       \
+            return ::b200vec::fail(#call, cudaGetErrorString(e__));                     \
+        }                                                                               \
+    } while (0)
+
+#define B2_REQUIRE(cond, msg)                                                           \
+    do {                                                                                \
+        if (!(cond)) return ::b200vec::fail(__func__, msg);                             \
+    } while (0)
+
+// A committed packet lives twice in HBM/L2 so that the placement kernel can always issue
+// 16-byte loads: copy A has y[0] on a 16-byte boundary (used when the first sample of a
+// float4 pair has an even packet index), copy B has y[0] 8 bytes past one (odd index).
+// Both copies are surrounded by >= kBankPad zero samples, so a pair that straddles either
+// end of the packet reads an exact 0 for the outside sample.
+constexpr int kBankPad = 4;
+
+struct BankSlot {
+    float2 *raw = nullptr;      // uploaded / resampled samples, len_raw
+    int64_t len_raw = 0, cap_raw = 0;
+    float2 *store = nullptr;    // backing store of copies A and B
+    int64_t cap_store = 0;      // capacity in samples PER COPY (excluding pads)
+    float2 *a = nullptr;        // -> y[0] of copy A (16-byte aligned)
+    float2 *b = nullptr;        // -> y[0] of copy B (8 mod 16)
+    int64_t len = 0;            // committed length (0 = not committed)
+};
+
+struct Scratch {
+    void *ptr = nullptr;
+    size_t bytes = 0;
+};
+
+}  // namespace b200vec
+
+struct b200vec_ctx {
+    int device = 0;
+    b200vec::BankSlot slots[B200VEC_MAX_SLOTS];
+    std::map<int, float2 *> twiddles;     // nfft -> exp(-2*pi*i*k/nfft), k < nfft/2 (float2)
+    b200vec::Scratch fft64[4];            // fp64 work buffers for the Bluestein resampler
+    unsigned int *hist = nullptr;         // select scratch (see select.cuh)
+    void *pinned = nullptr;               // small pinned staging block
+    int sm_count = b200vec::kSmCount;
+};

@@ -1,0 +1,226 @@
+"""Device engine: torch owns device memory and streams, libb200vec.so (hand-written sm_100a
+kernels behind the C-ABI of include/b200vec.h) does the arithmetic.
+
+One Engine per GPU (one process per GPU under torch.distributed).  Every method takes and
+returns torch CUDA tensors; the numpy-facing, reference-named API lives in api.py.  There is
+no CPU path: constructing an Engine without a CUDA device or without the built library
+raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib, hostmath as H
+from ._lib import BUILD_MAXONLY, BUILD_SCALE, BUILD_STORE, PktDesc, check
+
+
+class Engine:
+    def __init__(self, device=None):
+        if not torch.cuda.is_available():
+            raise _lib.B200VecError(
+                "vector_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.lib = _lib.load()
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None
+                                   else (device.index if isinstance(device, torch.device) else int(device)))
+        ctx = C.c_void_p()
+        check(self.lib.b200vec_create(self.device.index, C.byref(ctx)))
+        self._ctx = ctx
+        self._windows = {}
+        self._maxsq = torch.zeros(1, dtype=torch.float64, device=self.device)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.launches = 0          # kernels launched through this engine (bench.py's gpu_launches)
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self.lib.b200vec_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ helpers
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    @staticmethod
+    def _ptr(t):
+        return C.c_void_p(t.data_ptr())
+
+    # ------------------------------------------------------------------ packet bank
+    def bank_upload(self, slot, samples):
+        """samples: numpy complex64 [L] (host) or torch complex64 CUDA tensor."""
+        if isinstance(samples, torch.Tensor):
+            t = samples.to(self.device, torch.complex64).contiguous()
+            check(self.lib.b200vec_bank_upload(self._ctx, slot, self._ptr(t), t.numel(), 1, self._stream()))
+            torch.cuda.current_stream(self.device).synchronize()
+        else:
+            a = np.ascontiguousarray(samples, dtype=np.complex64)
+            check(self.lib.b200vec_bank_upload(self._ctx, slot, a.ctypes.data_as(C.c_void_p), a.size, 0,
+                                               self._stream()))
+            torch.cuda.current_stream(self.device).synchronize()   # `a` may be a temporary
+
+    def bank_resample(self, slot, n_out):
+        check(self.lib.b200vec_bank_resample(self._ctx, slot, int(n_out), self._stream()))
+
+    def bank_commit(self, slot, freq_hz=0.0, fs_hz=H.TARGET_SAMPLE_RATE):
+        check(self.lib.b200vec_bank_shift(self._ctx, slot, float(freq_hz), float(fs_hz), self._stream()))
+        self.launches += 1
+
+    def bank_len(self, slot):
+        n = C.c_int64()
+        check(self.lib.b200vec_bank_len(self._ctx, slot, C.byref(n)))
+        return n.value
+
+    def bank_download(self, slot):
+        n = self.bank_len(slot)
+        out = np.empty(n, dtype=np.complex64)
+        check(self.lib.b200vec_bank_download(self._ctx, slot, out.ctypes.data_as(C.c_void_p), n, self._stream()))
+        return out
+
+    # ------------------------------------------------------------------ vector build
+    @staticmethod
+    def make_descs(rows):
+        """rows: iterable of (start, period, count, slot) -> ctypes array of b200vec_pkt_desc."""
+        rows = list(rows)
+        arr = (PktDesc * max(1, len(rows)))()
+        for i, (start, period, count, slot) in enumerate(rows):
+            arr[i] = PktDesc(int(start), int(period), int(count), int(slot), 0)
+        return arr, len(rows)
+
+    def build_pass(self, descs, n_descs, lo, hi, out, mode, maxsq=None):
+        maxsq = self._maxsq if maxsq is None else maxsq
+        check(self.lib.b200vec_build(self._ctx, descs, n_descs, int(lo), int(hi),
+                                     self._ptr(out) if out is not None else None, mode,
+                                     self._ptr(maxsq), self._stream()))
+        self.launches += 1
+
+    def build_vector(self, rows, total, normalize=True, lo=0, hi=None, out=None, reduce_max=None):
+        """Samples [lo, hi) of the composite vector as a complex64 CUDA tensor.
+
+        normalize=True runs the two-pass recompute: pass A reduces max|v|^2 over the slab
+        (no stores), `reduce_max(tensor)` (if given) all-reduces that one double across
+        ranks, pass B recomputes and stores v * (1/max).  Returns (vector, maxsq tensor)."""
+        hi = total if hi is None else hi
+        n = hi - lo
+        if out is None:
+            out = torch.empty(max(n, 0), dtype=torch.complex64, device=self.device)
+        descs, nd = self.make_descs(rows)
+        if not normalize:
+            self.build_pass(descs, nd, lo, hi, out, BUILD_STORE)
+            return out, None
+        self._maxsq.zero_()
+        self.build_pass(descs, nd, lo, hi, None, BUILD_MAXONLY)
+        if reduce_max is not None:
+            reduce_max(self._maxsq)
+        self.build_pass(descs, nd, lo, hi, out, BUILD_SCALE)
+        return out, self._maxsq
+
+    # ------------------------------------------------------------------ spectrogram
+    def window(self, name, nperseg, fs, scaling):
+        key = (name, nperseg, float(fs), scaling)
+        if key not in self._windows:
+            taps, scale = H.window_and_scale(name, nperseg, fs, scaling)
+            self._windows[key] = (torch.from_numpy(taps.astype(np.float32)).to(self.device), float(scale))
+        return self._windows[key]
+
+    def stft(self, x, window, nperseg, noverlap, nfft, fs, scaling="density", stride=1,
+             in_origin=0, frame_lo=0, n_frames=None, total_len=None, out=None, flag=None):
+        """|STFT|^2*scale of x[::stride] -> float32 [nfft, n_frames], rows fftshifted.
+        x is a complex64 CUDA tensor whose element 0 is vector sample `in_origin`."""
+        hop = nperseg - noverlap
+        total_len = (in_origin + x.numel()) if total_len is None else total_len
+        n_dec = (total_len + stride - 1) // stride
+        if n_frames is None:
+            n_frames = 0 if n_dec < nperseg else (n_dec - nperseg) // hop + 1 - frame_lo
+        if out is None:
+            out = torch.empty((nfft, max(n_frames, 0)), dtype=torch.float32, device=self.device)
+        taps, scale = self.window(window, nperseg, fs, scaling)
+        check(self.lib.b200vec_stft(self._ctx, self._ptr(x), int(in_origin), x.numel(), int(stride),
+                                    int(nperseg), int(hop), int(nfft), self._ptr(taps), scale,
+                                    int(frame_lo), int(n_frames), self._ptr(out), out.stride(0),
+                                    self._ptr(flag) if flag is not None else None, self._stream()))
+        self.launches += 1
+        return out
+
+    # ------------------------------------------------------------------ dB / percentiles
+    def db(self, s, floor_val, out=None):
+        s = s.contiguous()
+        out = torch.empty_like(s) if out is None else out
+        check(self.lib.b200vec_db(self._ctx, self._ptr(s), s.numel(), float(floor_val), self._ptr(out),
+                                  self._stream()))
+        self.launches += 1
+        return out
+
+    def select_count(self, x, positive_only=False):
+        n = C.c_int64()
+        check(self.lib.b200vec_select_count(self._ctx, self._ptr(x), x.numel(), int(positive_only),
+                                            C.byref(n), self._stream()))
+        self.launches += 3
+        return n.value
+
+    def select_ranks(self, x, ranks, positive_only=False):
+        ranks = [int(r) for r in ranks]
+        arr = (C.c_int64 * len(ranks))(*ranks)
+        vals = (C.c_float * len(ranks))()
+        check(self.lib.b200vec_select_ranks(self._ctx, self._ptr(x), x.numel(), int(positive_only), arr,
+                                            len(ranks), vals, self._stream()))
+        self.launches += 7
+        return np.asarray(list(vals), dtype=np.float32)
+
+    def percentile(self, x, q, positive_only=False, count=None):
+        """np.percentile(x[x>0] if positive_only else x, q) for a float32 CUDA tensor,
+        bit-for-bit (exact order statistics + numpy's own float32 index/lerp arithmetic)."""
+        x = x.contiguous().view(-1)
+        if count is None:
+            count = self.select_count(x, positive_only) if positive_only else x.numel()
+        if count == 0:
+            return None
+        lo, hi, gamma = H.percentile_ranks(count, q, np.float32)
+        v = self.select_ranks(x, [lo, hi], positive_only)
+        return H.lerp(v[0], v[1], gamma)
+
+    def normalize_spectrogram(self, s, low_percentile=10.0, high_percentile=95.0, max_dynamic_range=25):
+        """Device form of utils.normalize_spectrogram (utils.py:356-404) for a float32 CUDA
+        tensor: returns (Sxx_db tensor, vmin, vmax)."""
+        flat = s.contiguous().view(-1)
+        floor_ = self.percentile(flat, 5, positive_only=True)
+        floor_ = 1e-12 if floor_ is None else floor_
+        floor_ = max(floor_, 1e-12)
+        db = self.db(flat, floor_).view(s.shape)
+        dflat = db.view(-1)
+        n = dflat.numel()
+        lo1, hi1, g1 = H.percentile_ranks(n, low_percentile, np.float32)
+        lo2, hi2, g2 = H.percentile_ranks(n, high_percentile, np.float32)
+        v = self.select_ranks(dflat, [lo1, hi1, lo2, hi2, 0, n - 1])
+        vmin, vmax = H.lerp(v[0], v[1], g1), H.lerp(v[2], v[3], g2)
+        vmin, vmax = H.colour_limits(vmin, vmax, v[4], v[5], max_dynamic_range)
+        return db, vmin, vmax
+
+    # ------------------------------------------------------------------ .wv payload
+    def wv_quantize(self, x, out=None):
+        x = x.contiguous()
+        out = torch.empty(2 * x.numel(), dtype=torch.int16, device=self.device) if out is None else out
+        check(self.lib.b200vec_wv_quantize(self._ctx, self._ptr(x), x.numel(), self._ptr(out), self._stream()))
+        self.launches += 1
+        return out
+
+
+_ENGINES = {}
+
+
+def get_engine(device=None):
+    """Process-wide Engine for `device` (default: torch's current CUDA device)."""
+    if not torch.cuda.is_available():
+        raise _lib.B200VecError(
+            "vector_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    idx = torch.cuda.current_device() if device is None else (
+        device.index if isinstance(device, torch.device) else int(device))
+    if idx not in _ENGINES:
+        _ENGINES[idx] = Engine(idx)
+    return _ENGINES[idx]
