@@ -170,3 +170,17 @@ def test_slab_and_frame_partition_cover_exactly_once():
                     if b > a:
                         assert lo <= a * hop * stride < hi or a == b
                         assert ((b - 1) * hop + nps - 1) * stride < halo <= total
+
+
+def test_product_synth_matches_oracle_synth():
+    """The product's scenario generator (vector_b200/synth.py) and the oracle's are separate
+    code; they must produce the same packets and tables."""
+    from vector_b200 import synth
+    for i, k in enumerate(synth.KINDS):
+        assert np.array_equal(synth.packet(k, seed=101 + i), O.synth_packet(k, seed=101 + i))
+    strip = lambda cs: [{k: v for k, v in c.items()} for c in cs]
+    assert strip(synth.configs(synth.CFG1_ROWS)) == strip(O.cfg1_configs())
+    assert strip(synth.configs(synth.CFG2_ROWS)) == strip(O.cfg2_configs())
+    cfgs, pk = synth.scenario(synth.CFG2_ROWS)
+    for (a, pa), (b, pb) in zip(pk, O.packets_for(O.cfg2_configs())):
+        assert pa == pb and np.array_equal(a, b)

@@ -1,0 +1,78 @@
+"""Multi-GPU form of the path: contiguous time-slab sharding, one process per GPU.
+
+The composite vector is a pure function of (packet bank, integer descriptors, sample index),
+so rank g fills samples [lo_g, hi_g) with no data-path communication; the packet bank (a few
+MB) is replicated.  The only exchange is the normalisation scalar: one double (max |v|^2)
+all-reduced with MAX between pass A and pass B — NCCL over NVLink/NVSwitch on GPUs, gloo in
+the CPU tests.  STFT frames belong to the rank that holds their first sample; the
+<= (nperseg-1)*stride trailing halo is recomputed locally by the placement kernel rather than
+exchanged.  The reference has no distributed code at all; this module is the
+"long vector" answer to what it handles by decimation (utils.py:184-200).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+from . import hostmath as H
+
+
+@dataclass(frozen=True)
+class SlabPlan:
+    rank: int
+    world: int
+    total: int
+    lo: int               # first owned sample
+    hi: int               # one past the last owned sample
+    frame_lo: int         # first owned STFT frame
+    frame_hi: int
+    halo_hi: int          # one past the last sample the owned frames read (>= hi)
+    n_frames_total: int
+
+
+def plan_slab(total, world, rank, nperseg=1024, hop=512, stride=1, align=16):
+    lo, hi = H.slab_bounds(total, world, rank, align)
+    n_dec = (total + stride - 1) // stride
+    nf = 0 if n_dec < nperseg else (n_dec - nperseg) // hop + 1
+    f_lo, f_hi, halo = H.frame_range_for_slab(lo, hi, total, stride, nperseg, hop, nf)
+    return SlabPlan(rank, world, total, lo, hi, f_lo, f_hi, halo, nf)
+
+
+def make_max_reducer(group=None):
+    """all-reduce(MAX) of the one-element max|v|^2 tensor; None when not distributed."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return None
+
+    def reduce_max(t):
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    return reduce_max
+
+
+def build_slab(engine, rows, plan, normalize=True, reduce_max=None, out=None):
+    """Owned slab plus halo of the (optionally normalised) vector on this rank's GPU.
+    The max is reduced over OWNED samples only (every sample is owned by exactly one rank),
+    the store pass also fills the halo.  Returns (tensor [halo_hi - lo], maxsq or None)."""
+    import torch
+    from ._lib import BUILD_MAXONLY, BUILD_SCALE, BUILD_STORE
+    n = plan.halo_hi - plan.lo
+    if out is None:
+        out = torch.empty(max(n, 0), dtype=torch.complex64, device=engine.device)
+    descs, nd = engine.make_descs(rows)
+    if not normalize:
+        engine.build_pass(descs, nd, plan.lo, plan.halo_hi, out, BUILD_STORE)
+        return out, None
+    engine._maxsq.zero_()
+    engine.build_pass(descs, nd, plan.lo, plan.hi, None, BUILD_MAXONLY)
+    if reduce_max is not None:
+        reduce_max(engine._maxsq)
+    engine.build_pass(descs, nd, plan.lo, plan.halo_hi, out, BUILD_SCALE)
+    return out, engine._maxsq
+
+
+def stft_slab(engine, vec, plan, window="hann", nperseg=1024, noverlap=512, nfft=1024, fs=56e6,
+              scaling="density", stride=1, out=None):
+    """This rank's columns [frame_lo, frame_hi) of the global spectrogram, computed from its
+    slab+halo tensor.  Columns concatenate in rank order."""
+    return engine.stft(vec, window, nperseg, noverlap, nfft, fs, scaling=scaling, stride=stride,
+                       in_origin=plan.lo, frame_lo=plan.frame_lo,
+                       n_frames=plan.frame_hi - plan.frame_lo, total_len=plan.total, out=out)
