@@ -21,6 +21,16 @@ def ulp_diff_f32(a, b):
     return float(np.max(np.abs(a - b) / scale)) if a.size else 0.0
 
 
+def max_err_rel_peak(got, want):
+    """max |got-want| / max |want|: the per-sample error relative to the vector's peak.  (ulps of
+    the individual samples are meaningless once packets are summed: cancellation leaves tiny
+    values whose last bits depend on 1-ulp differences in the operands.)"""
+    want = np.asarray(want)
+    peak = np.max(np.abs(want)) if want.size else 0.0
+    d = np.max(np.abs(np.asarray(got).astype(np.complex128) - want.astype(np.complex128))) if want.size else 0.0
+    return float(d / peak) if peak > 0 else float(d)
+
+
 def spec_db_error(S, S_ref, floor=SPEC_FLOOR):
     """max |10log10 S - 10log10 S_ref| over bins with S_ref >= peak*floor."""
     S, S_ref = np.asarray(S, np.float64), np.asarray(S_ref, np.float64)

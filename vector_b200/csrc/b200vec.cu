@@ -206,7 +206,7 @@ int b200vec_build(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
     B2_REQUIRE(n_pkts >= 0 && n_pkts <= B200VEC_MAX_PACKETS, "too many packets");
     B2_REQUIRE(n_pkts == 0 || descs, "descs is NULL");
     B2_REQUIRE(slab_lo >= 0 && slab_hi >= slab_lo, "bad slab");
-    B2_REQUIRE(mode == B200VEC_BUILD_MAXONLY || out_dev, "out_dev is NULL");
+    B2_REQUIRE(mode == B200VEC_BUILD_MAXONLY || out_dev || slab_hi == slab_lo, "out_dev is NULL");
     B2_REQUIRE(mode == B200VEC_BUILD_STORE || maxsq_dev, "maxsq_dev is NULL");
     B2_REQUIRE(((uintptr_t)out_dev & 15) == 0, "out_dev must be 16-byte aligned");
     PlaceArgs args;
@@ -242,6 +242,11 @@ int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_
     B2_REQUIRE(hop >= 1, "noverlap must be less than nperseg.");
     B2_REQUIRE(stride >= 1 && in_len >= 0 && n_frames >= 0 && out_ld >= n_frames, "bad geometry");
     if (n_frames == 0) return 0;
+    {   // every sample the requested frames read must lie inside in_dev[0, in_len)
+        const long long first = frame_lo * (long long)hop * stride - in_origin;
+        const long long last = ((frame_lo + n_frames - 1) * (long long)hop + nperseg - 1) * stride - in_origin;
+        B2_REQUIRE(frame_lo >= 0 && first >= 0 && last < in_len, "frames read outside the input buffer");
+    }
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     if (nfft == 1024 && stft1024_enabled()) {

@@ -95,6 +95,8 @@ class Engine:
 
     def build_pass(self, descs, n_descs, lo, hi, out, mode, maxsq=None):
         maxsq = self._maxsq if maxsq is None else maxsq
+        if hi <= lo:
+            return
         check(self.lib.b200vec_build(self._ctx, descs, n_descs, int(lo), int(hi),
                                      self._ptr(out) if out is not None else None, mode,
                                      self._ptr(maxsq), self._stream()))
