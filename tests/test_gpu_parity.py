@@ -245,6 +245,37 @@ def test_full_rate_stft_matches_oracle(eng, fast, monkeypatch):
     _check_spec(S.cpu().numpy(), Sr, St)
 
 
+@pytest.mark.parametrize("nperseg,noverlap,stride,win", [(1024, 512, 1, "hann"), (1024, 768, 1, "hann"),
+                                                         (1024, 0, 1, "blackmanharris"), (1024, 513, 1, "hann"),
+                                                         (1024, 1023, 1, "boxcar"), (1024, 990, 1, "hann"),
+                                                         (512, 412, 56, "hann"), (934, 0, 6, "hann"),
+                                                         (1000, 499, 3, "blackmanharris")])
+@pytest.mark.parametrize("tma", ["1", "0"])
+def test_stft1024_kernels_match_scipy(eng, nperseg, noverlap, stride, win, tma, monkeypatch):
+    """Both nfft-1024 kernels (TMA-staged and gather) over hops, strides and windows, odd origins."""
+    monkeypatch.setenv("B200VEC_STFT_TMA", tma)
+    rng = np.random.default_rng(nperseg + noverlap + stride)
+    n = 40_000 * stride + 7
+    t = np.arange(n) / 56e6
+    x = (np.exp(2j * np.pi * 3.3e6 * t / stride) + 1e-3 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))).astype(np.complex64)
+    d = torch.from_numpy(x).cuda()
+    fs = 56e6 / stride
+    S = eng.stft(d, win, nperseg, noverlap, 1024, fs, scaling="spectrum", stride=stride).cpu().numpy()
+    xs = x[::stride]
+    _, _, Sr = scipy.signal.spectrogram(xs, fs=fs, window=win, nperseg=nperseg, noverlap=noverlap, nfft=1024,
+                                        return_onesided=False, detrend=False, scaling="spectrum")
+    Sr = np.fft.fftshift(Sr, axes=0)
+    assert S.shape == Sr.shape
+    assert P.spec_db_error(S, Sr) <= P.SPEC_DB
+    # a slab-relative call (origin != 0, frame_lo != 0) gives the same columns
+    hop = nperseg - noverlap
+    f_lo = 5
+    origin = (f_lo * hop * stride) // 2 * 2
+    part = eng.stft(d[origin:], win, nperseg, noverlap, 1024, fs, scaling="spectrum", stride=stride,
+                    in_origin=origin, frame_lo=f_lo, n_frames=S.shape[1] - f_lo, total_len=n).cpu().numpy()
+    assert np.array_equal(part, S[:, f_lo:])
+
+
 def test_full_rate_stft_cfg1(eng):
     import vector_b200 as vb
     r = _build("cfg1_100ms", eng)

@@ -12,9 +12,15 @@
 // block's 16 frames are done every output row is written as one contiguous 64-byte run
 // (rows are the reference's fftshifted [nfft, frames] layout, frames are the fast axis).
 //
-// Per frame: one global read of the samples, one shared round trip, ~1.5 k warp instructions.
-// 111 616 B of shared memory and <= 128 registers per thread -> 2 CTAs (16 warps) per SM;
-// the grid is persistent: 2 x 148 CTAs stride over the frame tiles.
+// Two kernels share that FFT core:
+//   stft1024_tma_kernel    unit stride, nperseg = 1024, hop <= 512 (the full-rate BASELINE shape).
+//       One persistent 16-warp CTA per SM.  The (15*hop + 1024)-sample input span of the NEXT
+//       16-frame tile is fetched by one TMA bulk copy (cp.async.bulk -> mbarrier) while the
+//       current tile is transformed, so every input sample crosses HBM->SM exactly once and no
+//       warp ever waits on a global load; window taps live in registers.
+//   stft1024_gather_kernel any stride / nperseg <= 1024 / hop (the decimated preview of
+//       create_spectrogram, utils.py:192-195: a strided gather, the decimated copy is never
+//       materialised).  2 CTAs of 8 warps per SM, plain predicated loads.
 #pragma once
 #include "common.cuh"
 #include <utility>
@@ -24,7 +30,7 @@ namespace b200vec {
 constexpr int kS1Threads = 256;
 constexpr int kS1Warps = kS1Threads / 32;
 constexpr int kS1Frames = 16;                                  // frames per tile
-constexpr int kS1ExchPerWarp = 16 * 33;                        // float2: half of the (q, l) square, rows padded to 33
+constexpr int kS1ExchPerWarp = 16 * 33;                        // float2 units = one padded [32][33] float square
 constexpr size_t kS1TileBytes = 1024 * kS1Frames * sizeof(float);
 constexpr size_t kS1ExchBytes = (size_t)kS1Warps * kS1ExchPerWarp * sizeof(float2);
 constexpr size_t kS1TwBytes = 1024 * sizeof(float2);
@@ -95,9 +101,27 @@ __device__ __forceinline__ void fft32(float2 (&a)[32], float2 (&b)[32]) {
     s1_stage<16>(a, b, S{});
 }
 
-template <bool UNIT>       // UNIT: stride == 1 and nperseg == 1024 (no predicates, immediate offsets)
+// (l, q) swap across the warp: on entry lane l holds y[q] = B_l[q]; on exit lane q holds
+// x[l] = B_l[q].  Real parts, then imaginary parts, through one padded [32][33] float square:
+// every lane is active in every access, all accesses are conflict-free, and at most 64 data
+// registers are live at any point (the re halves die as they are stored).
+__device__ __forceinline__ void exchange_lq(float *e, int lane, const float2 (&y)[32], float2 (&x)[32]) {
+#pragma unroll
+    for (int q = 0; q < 32; ++q) e[q * 33 + lane] = y[q].x;
+    __syncwarp();
+#pragma unroll
+    for (int l = 0; l < 32; ++l) x[l].x = e[lane * 33 + l];
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < 32; ++q) e[q * 33 + lane] = y[q].y;
+    __syncwarp();
+#pragma unroll
+    for (int l = 0; l < 32; ++l) x[l].y = e[lane * 33 + l];
+    __syncwarp();
+}
+
 __global__ void __launch_bounds__(kS1Threads, 2)
-stft1024_kernel(const S1Args a) {
+stft1024_gather_kernel(const S1Args a) {
     extern __shared__ __align__(16) unsigned char s1_smem[];
     float *tile = reinterpret_cast<float *>(s1_smem);
     float2 *exch_all = reinterpret_cast<float2 *>(s1_smem + kS1TileBytes);
@@ -105,7 +129,7 @@ stft1024_kernel(const S1Args a) {
     float *win = reinterpret_cast<float *>(s1_smem + kS1TileBytes + kS1ExchBytes + kS1TwBytes);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    float2 *exch = exch_all + warp * kS1ExchPerWarp;
+    float *exch = reinterpret_cast<float *>(exch_all + warp * kS1ExchPerWarp);
     for (int i = tid; i < 1024; i += kS1Threads) {
         tw[i] = __ldg(a.tw + i);
         win[i] = (i < a.nperseg) ? __ldg(a.window + i) : 0.f;
@@ -124,16 +148,7 @@ stft1024_kernel(const S1Args a) {
             if (c >= nfr) continue;
             const long long f = a.frame_lo + f0 + c;
             float2 x[32], y[32];
-            if (UNIT) {
-                const float2 *p = a.in + (f * a.hop - a.in_origin) + lane;
-#pragma unroll
-                for (int j = 0; j < 32; ++j) x[j] = __ldg(p + 32 * j);
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const float w = win[lane + 32 * j];
-                    x[j].x *= w; x[j].y *= w;
-                }
-            } else {
+            {
                 const long long base = f * a.hop;
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
@@ -154,23 +169,7 @@ stft1024_kernel(const S1Args a) {
                 const float2 v = y[q];
                 y[q] = make_float2(v.x * w.x - v.y * w.y, v.x * w.y + v.y * w.x);
             }
-            // (l, q) swap through shared memory, q-halves in turn: lane q receives x[l] = y_l[q]
-#pragma unroll
-            for (int q = 0; q < 16; ++q) exch[q * 33 + lane] = y[q];
-            __syncwarp();
-            if (lane < 16) {
-#pragma unroll
-                for (int l = 0; l < 32; ++l) x[l] = exch[lane * 33 + l];
-            }
-            __syncwarp();
-#pragma unroll
-            for (int q = 16; q < 32; ++q) exch[(q - 16) * 33 + lane] = y[q];
-            __syncwarp();
-            if (lane >= 16) {
-#pragma unroll
-                for (int l = 0; l < 32; ++l) x[l] = exch[(lane - 16) * 33 + l];
-            }
-            __syncwarp();
+            exchange_lq(exch, lane, y, x);                  // lane q receives x[l] = y_l[q]
             fft32(x, y);                                    // y[s] = X[lane + 32 s]
             const int col = c ^ swz;
 #pragma unroll
@@ -199,9 +198,135 @@ stft1024_kernel(const S1Args a) {
     if (a.flag && __syncthreads_or(any) && tid == 0) atomicOr(a.flag, 1);
 }
 
+// ---- TMA / mbarrier primitives (sm_90+ PTX; SASS: UBLKCP / SYNCS) -------------------------
+__device__ __forceinline__ unsigned smem_u32(const void *p) {
+    return static_cast<unsigned>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(unsigned mbar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned mbar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(mbar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+}
+
+constexpr int kT1Threads = 512;                                   // 16 warps: one frame each per tile
+constexpr int kT1Warps = kT1Threads / 32;
+constexpr int kT1MaxSpan = (kS1Frames - 1) * 512 + 1024;          // input samples per tile at hop <= 512
+constexpr size_t kT1ExchBytes = (size_t)kT1Warps * 32 * 33 * sizeof(float);
+constexpr size_t kT1StageBytes = (size_t)kT1MaxSpan * sizeof(float2);
+constexpr size_t kT1OffExch = kS1TileBytes;
+constexpr size_t kT1OffTw = kT1OffExch + kT1ExchBytes;
+constexpr size_t kT1OffStage = kT1OffTw + kS1TwBytes;
+constexpr size_t kT1OffBar = kT1OffStage + kT1StageBytes;
+constexpr size_t kT1Smem = kT1OffBar + 16;                        // 64 K + 66 K + 8 K + 68 K = 211 216 B
+
+__device__ __forceinline__ void t1_issue_tile(const S1Args &a, long long tile, unsigned stage, unsigned mbar) {
+    const long long f0 = tile * kS1Frames;
+    const int nfr = (int)((a.n_frames - f0 < kS1Frames) ? (a.n_frames - f0) : kS1Frames);
+    const unsigned bytes = (unsigned)(((nfr - 1) * a.hop + 1024) * sizeof(float2));
+    const char *src = reinterpret_cast<const char *>(a.in + ((a.frame_lo + f0) * a.hop - a.in_origin));
+    mbar_expect_tx(mbar, bytes);
+    for (unsigned off = 0; off < bytes; off += 16384) {           // a few <= 16 KB bulk copies, one barrier
+        const unsigned n = (bytes - off < 16384u) ? (bytes - off) : 16384u;
+        tma_bulk_g2s(stage + off, src + off, n, mbar);
+    }
+}
+
+__global__ void __launch_bounds__(kT1Threads, 1)
+stft1024_tma_kernel(const S1Args a) {
+    extern __shared__ __align__(128) unsigned char t1_smem[];
+    float *tile = reinterpret_cast<float *>(t1_smem);
+    float2 *tw = reinterpret_cast<float2 *>(t1_smem + kT1OffTw);
+    const float2 *stage = reinterpret_cast<const float2 *>(t1_smem + kT1OffStage);
+    const unsigned stage_u32 = smem_u32(t1_smem + kT1OffStage);
+    const unsigned mbar = smem_u32(t1_smem + kT1OffBar);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float *exch = reinterpret_cast<float *>(t1_smem + kT1OffExch) + warp * (32 * 33);
+    for (int i = tid; i < 1024; i += kT1Threads) tw[i] = __ldg(a.tw + i);
+    float wreg[32];                                               // this lane's window taps, resident
+#pragma unroll
+    for (int j = 0; j < 32; ++j) wreg[j] = __ldg(a.window + lane + 32 * j);
+    const long long n_tiles = (a.n_frames + kS1Frames - 1) / kS1Frames;
+    if (tid == 0) {
+        mbar_init(mbar, 1);
+        if ((long long)blockIdx.x < n_tiles) t1_issue_tile(a, blockIdx.x, stage_u32, mbar);
+    }
+    __syncthreads();
+
+    int any = 0;
+    unsigned parity = 0;
+    const int swz = (lane >> 1) & 15;
+    const int c = warp;                                           // tile column = frame within the tile
+    for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const long long f0 = t * kS1Frames;
+        const int nfr = (int)((a.n_frames - f0 < kS1Frames) ? (a.n_frames - f0) : kS1Frames);
+        float2 x[32], y[32];
+        mbar_wait(mbar, parity);                                  // this tile's samples have landed
+        parity ^= 1;
+        if (c < nfr) {
+            const float2 *p = stage + c * a.hop + lane;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const float2 v = p[32 * j];
+                x[j] = make_float2(v.x * wreg[j], v.y * wreg[j]);
+            }
+        }
+        __syncthreads();                                          // staging and PSD tile are both free now
+        if (tid == 0 && t + gridDim.x < n_tiles) t1_issue_tile(a, t + gridDim.x, stage_u32, mbar);
+        if (c < nfr) {
+            fft32(x, y);                                          // y[q] = sum_j x[l + 32 j] W32^(j q)
+#pragma unroll
+            for (int q = 1; q < 32; ++q) {                        // times W1024^(l q)
+                const float2 w = tw[q * 32 + lane];
+                const float2 v = y[q];
+                y[q] = make_float2(v.x * w.x - v.y * w.y, v.x * w.y + v.y * w.x);
+            }
+            exchange_lq(exch, lane, y, x);
+            fft32(x, y);                                          // y[s] = X[lane + 32 s]
+            const int col = c ^ swz;
+#pragma unroll
+            for (int s = 0; s < 32; ++s) {
+                const float p = (y[s].x * y[s].x + y[s].y * y[s].y) * a.scale;
+                any |= (p != 0.f);
+                const int row = lane + 32 * ((s + 16) & 31);      // fftshift
+                tile[row * kS1Frames + col] = p;
+            }
+        }
+        __syncthreads();                                          // tile complete
+        {
+            const int cc = tid & (kS1Frames - 1);
+            const int r0 = tid / kS1Frames;                       // 0..31
+            if (cc < nfr) {
+                float *o = a.out + f0 + cc;
+#pragma unroll 8
+                for (int i = 0; i < 1024 / (kT1Threads / kS1Frames); ++i) {
+                    const int r = r0 + (kT1Threads / kS1Frames) * i;
+                    __stcs(o + (long long)r * a.out_ld, tile[r * kS1Frames + (cc ^ ((r >> 1) & 15))]);
+                }
+            }
+        }
+    }
+    if (a.flag && __syncthreads_or(any) && tid == 0) atomicOr(a.flag, 1);
+}
+
 inline int stft1024_setup() {
-    B2_CUDA(cudaFuncSetAttribute(stft1024_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kS1Smem));
-    B2_CUDA(cudaFuncSetAttribute(stft1024_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kS1Smem));
+    B2_CUDA(cudaFuncSetAttribute(stft1024_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kS1Smem));
+    B2_CUDA(cudaFuncSetAttribute(stft1024_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT1Smem));
     return 0;
 }
 
@@ -239,13 +364,17 @@ inline int launch_stft1024(b200vec_ctx *ctx, const float2 *in, long long in_orig
     a.out = out; a.out_ld = out_ld; a.flag = flag;
     if (get_tw1024(ctx, &a.tw)) return 1;
     const long long n_tiles = (n_frames + kS1Frames - 1) / kS1Frames;
-    long long grid = n_tiles;
-    const long long cap = 2LL * ctx->sm_count;              // persistent: 2 resident CTAs per SM
-    if (grid > cap) grid = cap;
-    if (stride == 1 && nperseg == 1024)
-        stft1024_kernel<true><<<(unsigned)grid, kS1Threads, kS1Smem, st>>>(a);
-    else
-        stft1024_kernel<false><<<(unsigned)grid, kS1Threads, kS1Smem, st>>>(a);
+    const char *no_tma = getenv("B200VEC_STFT_TMA");          // "0" forces the gather kernel (A/B tests)
+    const long long first = frame_lo * (long long)hop - in_origin;
+    const bool tma_ok = stride == 1 && nperseg == 1024 && hop <= 512 && (hop & 1) == 0 &&
+                        ((reinterpret_cast<uintptr_t>(in + first)) & 15) == 0 && !(no_tma && no_tma[0] == '0');
+    if (tma_ok) {
+        long long grid = n_tiles < ctx->sm_count ? n_tiles : ctx->sm_count;      // persistent, 1 CTA per SM
+        stft1024_tma_kernel<<<(unsigned)grid, kT1Threads, kT1Smem, st>>>(a);
+    } else {
+        long long grid = n_tiles < 2LL * ctx->sm_count ? n_tiles : 2LL * ctx->sm_count;
+        stft1024_gather_kernel<<<(unsigned)grid, kS1Threads, kS1Smem, st>>>(a);
+    }
     B2_CUDA(cudaGetLastError());
     return 0;
 }
