@@ -150,7 +150,7 @@ def run_ours(args):
     plan = vdist.plan_slab(total, world, rank, 1024, 512, 1)
     n_local = plan.halo_hi - plan.lo
     vec = torch.empty(n_local, dtype=torch.complex64, device=eng.device)
-    spec = torch.empty((1024, plan.frame_hi - plan.frame_lo), dtype=torch.float32, device=eng.device)
+    spec = eng.alloc_spectrogram(1024, plan.frame_hi - plan.frame_lo)
     descs, nd = eng.make_descs(rows)
     from vector_b200._lib import BUILD_MAXONLY, BUILD_SCALE
 

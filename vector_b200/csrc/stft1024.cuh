@@ -223,20 +223,23 @@ __device__ __forceinline__ void tma_bulk_g2s(unsigned dst, const void *src, unsi
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
 }
 
-constexpr int kT1Threads = 512;                                   // 16 warps: one frame each per tile
-constexpr int kT1Warps = kT1Threads / 32;
-constexpr int kT1MaxSpan = (kS1Frames - 1) * 512 + 1024;          // input samples per tile at hop <= 512
-constexpr size_t kT1ExchBytes = (size_t)kT1Warps * 32 * 33 * sizeof(float);
-constexpr size_t kT1StageBytes = (size_t)kT1MaxSpan * sizeof(float2);
-constexpr size_t kT1OffExch = kS1TileBytes;
-constexpr size_t kT1OffTw = kT1OffExch + kT1ExchBytes;
-constexpr size_t kT1OffStage = kT1OffTw + kS1TwBytes;
-constexpr size_t kT1OffBar = kT1OffStage + kT1StageBytes;
-constexpr size_t kT1Smem = kT1OffBar + 16;                        // 64 K + 66 K + 8 K + 68 K = 211 216 B
+// Shared-memory plan of stft1024_tma_kernel<W>: W warps, W frames per tile (one per warp).
+template <int W>
+struct T1 {
+    static constexpr int kThreads = 32 * W;
+    static constexpr int kSpan = (W - 1) * 512 + 1024;                 // input samples per tile at hop <= 512
+    static constexpr size_t kTile = (size_t)1024 * W * sizeof(float);  // PSD tile [1024 rows][W frames]
+    static constexpr size_t kOffExch = kTile;
+    static constexpr size_t kOffTw = kOffExch + (size_t)W * 32 * 33 * sizeof(float);
+    static constexpr size_t kOffStage = kOffTw + kS1TwBytes;
+    static constexpr size_t kOffBar = kOffStage + (size_t)kSpan * sizeof(float2);
+    static constexpr size_t kSmem = kOffBar + 16;      // W=16: 211 216 B (1 CTA/SM); W=8: 111 632 B (2 CTAs/SM)
+};
 
+template <int W>
 __device__ __forceinline__ void t1_issue_tile(const S1Args &a, long long tile, unsigned stage, unsigned mbar) {
-    const long long f0 = tile * kS1Frames;
-    const int nfr = (int)((a.n_frames - f0 < kS1Frames) ? (a.n_frames - f0) : kS1Frames);
+    const long long f0 = tile * W;
+    const int nfr = (int)((a.n_frames - f0 < W) ? (a.n_frames - f0) : W);
     const unsigned bytes = (unsigned)(((nfr - 1) * a.hop + 1024) * sizeof(float2));
     const char *src = reinterpret_cast<const char *>(a.in + ((a.frame_lo + f0) * a.hop - a.in_origin));
     mbar_expect_tx(mbar, bytes);
@@ -246,35 +249,43 @@ __device__ __forceinline__ void t1_issue_tile(const S1Args &a, long long tile, u
     }
 }
 
-__global__ void __launch_bounds__(kT1Threads, 1)
+template <int W>
+__global__ void __launch_bounds__(32 * W, 16 / W)
 stft1024_tma_kernel(const S1Args a) {
+    using L = T1<W>;
+    constexpr int kRowsPerPass = L::kThreads / W;                 // = 32
+    constexpr int kSwzShift = (W == 16) ? 1 : 2;                  // rows per bank group: 32 / W
     extern __shared__ __align__(128) unsigned char t1_smem[];
     float *tile = reinterpret_cast<float *>(t1_smem);
-    float2 *tw = reinterpret_cast<float2 *>(t1_smem + kT1OffTw);
-    const float2 *stage = reinterpret_cast<const float2 *>(t1_smem + kT1OffStage);
-    const unsigned stage_u32 = smem_u32(t1_smem + kT1OffStage);
-    const unsigned mbar = smem_u32(t1_smem + kT1OffBar);
+    float2 *tw = reinterpret_cast<float2 *>(t1_smem + L::kOffTw);
+    const float2 *stage = reinterpret_cast<const float2 *>(t1_smem + L::kOffStage);
+    const unsigned stage_u32 = smem_u32(t1_smem + L::kOffStage);
+    const unsigned mbar = smem_u32(t1_smem + L::kOffBar);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    float *exch = reinterpret_cast<float *>(t1_smem + kT1OffExch) + warp * (32 * 33);
-    for (int i = tid; i < 1024; i += kT1Threads) tw[i] = __ldg(a.tw + i);
+    float *exch = reinterpret_cast<float *>(t1_smem + L::kOffExch) + warp * (32 * 33);
+    for (int i = tid; i < 1024; i += L::kThreads) tw[i] = __ldg(a.tw + i);
     float wreg[32];                                               // this lane's window taps, resident
 #pragma unroll
     for (int j = 0; j < 32; ++j) wreg[j] = __ldg(a.window + lane + 32 * j);
-    const long long n_tiles = (a.n_frames + kS1Frames - 1) / kS1Frames;
+    const long long n_tiles = (a.n_frames + W - 1) / W;
     if (tid == 0) {
         mbar_init(mbar, 1);
-        if ((long long)blockIdx.x < n_tiles) t1_issue_tile(a, blockIdx.x, stage_u32, mbar);
+        if ((long long)blockIdx.x < n_tiles) t1_issue_tile<W>(a, blockIdx.x, stage_u32, mbar);
     }
     __syncthreads();
 
-    int any = 0;
+    unsigned anybits = 0;
     unsigned parity = 0;
-    const int swz = (lane >> 1) & 15;
     const int c = warp;                                           // tile column = frame within the tile
+    float *tile_w = tile + lane * W + (c ^ ((lane >> kSwzShift) & (W - 1)));          // + 32*W*rowblock
+    const int cc = tid & (W - 1);
+    const int r0 = tid / W;                                       // 0..31
+    const float *tile_r = tile + r0 * W + (cc ^ ((r0 >> kSwzShift) & (W - 1)));       // + 32*W*i
+    const long long out_step = (long long)kRowsPerPass * a.out_ld;
     for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const long long f0 = t * kS1Frames;
-        const int nfr = (int)((a.n_frames - f0 < kS1Frames) ? (a.n_frames - f0) : kS1Frames);
+        const long long f0 = t * W;
+        const int nfr = (int)((a.n_frames - f0 < W) ? (a.n_frames - f0) : W);
         float2 x[32], y[32];
         mbar_wait(mbar, parity);                                  // this tile's samples have landed
         parity ^= 1;
@@ -287,7 +298,7 @@ stft1024_tma_kernel(const S1Args a) {
             }
         }
         __syncthreads();                                          // staging and PSD tile are both free now
-        if (tid == 0 && t + gridDim.x < n_tiles) t1_issue_tile(a, t + gridDim.x, stage_u32, mbar);
+        if (tid == 0 && t + gridDim.x < n_tiles) t1_issue_tile<W>(a, t + gridDim.x, stage_u32, mbar);
         if (c < nfr) {
             fft32(x, y);                                          // y[q] = sum_j x[l + 32 j] W32^(j q)
 #pragma unroll
@@ -298,35 +309,32 @@ stft1024_tma_kernel(const S1Args a) {
             }
             exchange_lq(exch, lane, y, x);
             fft32(x, y);                                          // y[s] = X[lane + 32 s]
-            const int col = c ^ swz;
 #pragma unroll
-            for (int s = 0; s < 32; ++s) {
-                const float p = (y[s].x * y[s].x + y[s].y * y[s].y) * a.scale;
-                any |= (p != 0.f);
-                const int row = lane + 32 * ((s + 16) & 31);      // fftshift
-                tile[row * kS1Frames + col] = p;
+            for (int s = 0; s < 32; s += 2) {
+                const float p0 = (y[s].x * y[s].x + y[s].y * y[s].y) * a.scale;
+                const float p1 = (y[s + 1].x * y[s + 1].x + y[s + 1].y * y[s + 1].y) * a.scale;
+                anybits |= __float_as_uint(p0) | __float_as_uint(p1);     // p >= 0 or NaN: nonzero bits <=> p != 0
+                tile_w[32 * W * ((s + 16) & 31)] = p0;            // row = lane + 32*((s+16)&31): the fftshift
+                tile_w[32 * W * ((s + 17) & 31)] = p1;
             }
         }
         __syncthreads();                                          // tile complete
-        {
-            const int cc = tid & (kS1Frames - 1);
-            const int r0 = tid / kS1Frames;                       // 0..31
-            if (cc < nfr) {
-                float *o = a.out + f0 + cc;
+        if (cc < nfr) {
+            float *o = a.out + f0 + cc + (long long)r0 * a.out_ld;
 #pragma unroll 8
-                for (int i = 0; i < 1024 / (kT1Threads / kS1Frames); ++i) {
-                    const int r = r0 + (kT1Threads / kS1Frames) * i;
-                    __stcs(o + (long long)r * a.out_ld, tile[r * kS1Frames + (cc ^ ((r >> 1) & 15))]);
-                }
+            for (int i = 0; i < 1024 / kRowsPerPass; ++i) {
+                __stcs(o, tile_r[32 * W * i]);
+                o += out_step;
             }
         }
     }
-    if (a.flag && __syncthreads_or(any) && tid == 0) atomicOr(a.flag, 1);
+    if (a.flag && __syncthreads_or(anybits != 0) && tid == 0) atomicOr(a.flag, 1);
 }
 
 inline int stft1024_setup() {
     B2_CUDA(cudaFuncSetAttribute(stft1024_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kS1Smem));
-    B2_CUDA(cudaFuncSetAttribute(stft1024_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT1Smem));
+    B2_CUDA(cudaFuncSetAttribute(stft1024_tma_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T1<16>::kSmem));
+    B2_CUDA(cudaFuncSetAttribute(stft1024_tma_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T1<8>::kSmem));
     return 0;
 }
 
@@ -369,8 +377,16 @@ inline int launch_stft1024(b200vec_ctx *ctx, const float2 *in, long long in_orig
     const bool tma_ok = stride == 1 && nperseg == 1024 && hop <= 512 && (hop & 1) == 0 &&
                         ((reinterpret_cast<uintptr_t>(in + first)) & 15) == 0 && !(no_tma && no_tma[0] == '0');
     if (tma_ok) {
-        long long grid = n_tiles < ctx->sm_count ? n_tiles : ctx->sm_count;      // persistent, 1 CTA per SM
-        stft1024_tma_kernel<<<(unsigned)grid, kT1Threads, kT1Smem, st>>>(a);
+        const char *wsel = getenv("B200VEC_STFT_W");           // "8": two 8-warp CTAs per SM (A/B tests); default one 16-warp CTA
+        if (wsel && wsel[0] == '8') {
+            const long long nt = (n_frames + 7) / 8;
+            long long grid = nt < 2LL * ctx->sm_count ? nt : 2LL * ctx->sm_count;
+            stft1024_tma_kernel<8><<<(unsigned)grid, 256, T1<8>::kSmem, st>>>(a);
+        } else {                                               // measured on B200: 277 us vs 293 us at 56 M samples
+            const long long nt = (n_frames + 15) / 16;
+            long long grid = nt < ctx->sm_count ? nt : ctx->sm_count;
+            stft1024_tma_kernel<16><<<(unsigned)grid, 512, T1<16>::kSmem, st>>>(a);
+        }
     } else {
         long long grid = n_tiles < 2LL * ctx->sm_count ? n_tiles : 2LL * ctx->sm_count;
         stft1024_gather_kernel<<<(unsigned)grid, kS1Threads, kS1Smem, st>>>(a);

@@ -131,6 +131,12 @@ class Engine:
             self._windows[key] = (torch.from_numpy(taps.astype(np.float32)).to(self.device), float(scale))
         return self._windows[key]
 
+    def alloc_spectrogram(self, nfft, n_frames):
+        """float32 [nfft, n_frames] view whose rows start on 128-byte boundaries (row pitch
+        rounded up to 32 floats), so the kernels' per-row runs never straddle sectors."""
+        pitch = (n_frames + 31) // 32 * 32
+        return torch.empty((nfft, max(pitch, 32)), dtype=torch.float32, device=self.device)[:, :n_frames]
+
     def stft(self, x, window, nperseg, noverlap, nfft, fs, scaling="density", stride=1,
              in_origin=0, frame_lo=0, n_frames=None, total_len=None, out=None, flag=None):
         """|STFT|^2*scale of x[::stride] -> float32 [nfft, n_frames], rows fftshifted.
@@ -141,7 +147,7 @@ class Engine:
         if n_frames is None:
             n_frames = 0 if n_dec < nperseg else (n_dec - nperseg) // hop + 1 - frame_lo
         if out is None:
-            out = torch.empty((nfft, max(n_frames, 0)), dtype=torch.float32, device=self.device)
+            out = self.alloc_spectrogram(nfft, max(n_frames, 0))
         taps, scale = self.window(window, nperseg, fs, scaling)
         check(self.lib.b200vec_stft(self._ctx, self._ptr(x), int(in_origin), x.numel(), int(stride),
                                     int(nperseg), int(hop), int(nfft), self._ptr(taps), scale,
