@@ -4,8 +4,8 @@
 
 One step = one pass of the hot path over one batch of synthetic input:
     pass A (max |v|^2, no stores) -> [all-reduce MAX of one double when N > 1] ->
-    pass B (recompute, scale, store complex64) -> full-rate STFT (hann 1024/512, nfft 1024,
-    'density', fftshifted float32 [1024, frames])
+    ONE fused kernel: recompute, scale, store complex64 AND the full-rate STFT (hann 1024/512,
+    nfft 1024, 'density', fftshifted float32 [1024, frames]) out of shared memory
 on SURVEY.md §8d cfg2 (6 packets, periods 100/50/20/10/5/2 ms, shifts +2/-3/+1/-8/+6/-12 MHz,
 normalisation on).  At N GPUs the vector is N x 1000 ms long and time-sharded, 56 M samples
 (+ halo) per GPU: per-GPU work is fixed -> "scaling": "weak".  value = all samples / max-over-
@@ -147,10 +147,11 @@ def run_ours(args):
 
     info = generate.prepare_bank(eng, cfgs, packets, FS)
     rows = generate.placement_rows(cfgs, info, total, FS)
-    plan = vdist.plan_slab(total, world, rank, 1024, 512, 1)
-    n_local = plan.halo_hi - plan.lo
-    vec = torch.empty(n_local, dtype=torch.complex64, device=eng.device)
-    spec = eng.alloc_spectrogram(1024, plan.frame_hi - plan.frame_lo)
+    plan = vdist.plan_slab(total, world, rank, 1024, 512, 1, align=512)     # slabs cut on hop boundaries
+    n_own = plan.hi - plan.lo
+    n_frames = plan.frame_hi - plan.frame_lo
+    vec = torch.empty(n_own, dtype=torch.complex64, device=eng.device)
+    spec = eng.alloc_spectrogram(1024, n_frames)
     descs, nd = eng.make_descs(rows)
     from vector_b200._lib import BUILD_MAXONLY, BUILD_SCALE
 
@@ -158,18 +159,17 @@ def run_ours(args):
     marks = []
 
     def step(record=None):
-        e = [ev() for _ in range(4)] if record is not None else None
+        e = [ev() for _ in range(3)] if record is not None else None
         eng._maxsq.zero_()
         if e: e[0].record()
-        eng.build_pass(descs, nd, plan.lo, plan.hi, None, BUILD_MAXONLY)
-        if e: e[1].record()
+        eng.build_pass(descs, nd, plan.lo, plan.hi, None, BUILD_MAXONLY)            # pass A: max |v|^2, no stores
         if reduce_max is not None:
-            reduce_max(eng._maxsq)
-        eng.build_pass(descs, nd, plan.lo, plan.halo_hi, vec, BUILD_SCALE)
-        if e: e[2].record()
-        vdist.stft_slab(eng, vec, plan, fs=FS, out=spec)
+            reduce_max(eng._maxsq)                                                  # the one collective: 1 double, MAX
+        if e: e[1].record()
+        eng.build_stft1024(descs, nd, plan.lo, plan.hi, vec, BUILD_SCALE, plan.frame_lo, n_frames, spec,
+                           window="hann", fs=FS, scaling="density")                # place + scale + store + STFT
         if e:
-            e[3].record()
+            e[2].record()
             record.append(e)
 
     def barrier():
@@ -199,26 +199,20 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
     ms_step = ms_t.item() / args.steps
-    k_ms = np.array([[m[i].elapsed_time(m[i + 1]) for i in range(3)] for m in marks]).mean(axis=0)
+    k_ms = np.array([[m[i].elapsed_time(m[i + 1]) for i in range(2)] for m in marks]).mean(axis=0)
 
     # ---- e2e through the host-buffer API: H2D packets, D2H vector + spectrogram, every step
     pinned_pk = [(torch.from_numpy(np.ascontiguousarray(y)).pin_memory(), pre) for y, pre in packets]
-    out_vec = torch.empty(plan.hi - plan.lo, dtype=torch.complex64).pin_memory()
+    out_vec = torch.empty(n_own, dtype=torch.complex64).pin_memory()
     out_spec = torch.empty(spec.shape, dtype=torch.float32).pin_memory()
-    copy_stream = torch.cuda.Stream(device=eng.device)
 
     def e2e_step():
         pk = [(t.numpy(), pre) for t, pre in pinned_pk]
         generate.prepare_bank(eng, cfgs, pk, FS)                          # H2D of every packet + shift
-        v, _ = vdist.build_slab(eng, rows, plan, True, reduce_max, out=vec)
-        done = torch.cuda.Event(); done.record()
-        with torch.cuda.stream(copy_stream):                              # vector D2H overlaps the STFT
-            copy_stream.wait_event(done)
-            out_vec.copy_(v[: plan.hi - plan.lo], non_blocking=True)
-        s = vdist.stft_slab(eng, v, plan, fs=FS, out=spec)
+        v, s, _ = vdist.build_stft_slab(eng, rows, plan, True, reduce_max, fs=FS, out_vec=vec, out_spec=spec)
+        out_vec.copy_(v, non_blocking=True)
         out_spec.copy_(s, non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        copy_stream.synchronize()
         return float(out_spec[512, 0]) + float(out_vec[0].real)          # read the result on the host
 
     e2e_steps = max(2, min(args.steps, 5))
@@ -236,15 +230,17 @@ def run_ours(args):
 
     if rank == 0:
         peak, peak_src = peaks()
-        n_own = plan.hi - plan.lo
+        fused_bytes = 8 * n_own + 4 * spec.numel()
         kernels = {
-            "place_max(passA)": {"ms": k_ms[0], "alg_bytes": 0, "note": "no HBM output; L2-resident bank reads only"},
-            "place_scale_store(passB)": {"ms": k_ms[1], "alg_bytes": 8 * n_local},
-            "stft1024": {"ms": k_ms[2], "alg_bytes": 8 * n_local + 4 * spec.numel()},
+            "place_max(passA)": {"ms": k_ms[0], "alg_bytes": 0,
+                                 "note": "no HBM output; L2-resident bank reads only" + (
+                                     "; includes the 1-double all-reduce" if world > 1 else "")},
+            "build_stft1024(fused passB+STFT)": {"ms": k_ms[1], "alg_bytes": fused_bytes,
+                                                 "note": "8 B/Sa vector store + 8 B/Sa spectrogram store, nothing read"},
         }
         for k in kernels.values():
             k["GBps"] = k["alg_bytes"] / (k["ms"] * 1e-3) / 1e9 if k["ms"] > 0 else None
-        dom = max(("place_scale_store(passB)", "stft1024"), key=lambda k: kernels[k]["ms"])
+        dom = "build_stft1024(fused passB+STFT)"
         ach = kernels[dom]["GBps"]
         line = {
             "metric": METRIC, "value": total / (ms_step * 1e-3) / 1e9, "unit": "GSa/s", "n_gpus": world,
@@ -257,11 +253,11 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_nominal_8000": ach / 8000.0, "traffic": None,
                          "peak_source": peak_src,
-                         "step_frac": (8 * n_local + kernels["stft1024"]["alg_bytes"]) / (ms_step * 1e-3) / 1e9 / peak},
+                         "step_frac": fused_bytes / (ms_step * 1e-3) / 1e9 / peak},
             "kernels": kernels,
             "e2e": {"value": total / (e2e_ms.item() * 1e-3) / 1e9, "unit": "GSa/s", "ms_per_step": e2e_ms.item(),
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                    "api": "generate.prepare_bank + dist.build_slab + dist.stft_slab, pinned host buffers"},
+                    "api": "generate.prepare_bank + dist.build_stft_slab, pinned host buffers"},
             "gpu_launches": launches, "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:

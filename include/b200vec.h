@@ -109,6 +109,23 @@ int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_
                  int64_t frame_lo, int64_t n_frames, float *out_dev, int64_t out_ld,
                  int *nonzero_flag_dev, void *stream);
 
+/* ---- fused build + full-rate spectrogram (the BASELINE cfg2 + cfg3 step in ONE kernel) -----
+ * Pass B of b200vec_build (mode STORE or SCALE) and b200vec_stft for the fixed analysis shape of
+ * vector_analyzer/spectrogram_analysis.py:35-49 (nperseg = nfft = 1024, hop = 512, stride 1,
+ * two-sided, fftshifted rows) without re-reading the vector: a thread block places the samples of
+ * 16 frames (unified_gui.py:1757-1769,1781), streams them to vec_out_dev and transforms them out
+ * of shared memory.  HBM traffic 16 B per output sample (8 vector + 8 spectrogram), no reads.
+ *   vec_out_dev[0 .. slab_hi-slab_lo) receives samples [slab_lo, slab_hi);
+ *   frames [frame_lo, frame_lo+n_frames) go to spec_out_dev[row*out_ld + (f-frame_lo)];
+ *   slab_lo must equal frame_lo*512 (slabs are cut on hop boundaries) and every frame must start
+ *   inside the slab; samples past slab_hi that the last frames need (the <= 512-sample halo) are
+ *   computed but not stored.  SCALE reads *maxsq_dev exactly like b200vec_build. */
+int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                           int64_t slab_lo, int64_t slab_hi, void *vec_out_dev, int mode,
+                           double *maxsq_dev, const float *window_dev, float scale,
+                           int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                           int *nonzero_flag_dev, void *stream);
+
 /* ---- dB map and order statistics (normalize_spectrogram, utils.py:356-404) -----------
  * db      : out[i] = 10*log10(|s[i]| + floor)                      (utils.py:363-368)
  * select  : exact order statistics of a float32 array: ranks[] are 0-based positions in the

@@ -286,6 +286,116 @@ def test_full_rate_stft_cfg1(eng):
     _check_spec(S.cpu().numpy(), Sr, St)
 
 
+# ------------------------------------------------------------------------------ fused build + STFT
+def _fused(eng, cfgs, pk, n, normalize, world=1, rank=0):
+    from vector_b200 import dist as vdist, generate
+    info = generate.prepare_bank(eng, cfgs, pk, 56e6)
+    rows = generate.placement_rows(cfgs, info, n, 56e6)
+    plan = vdist.plan_slab(n, world, rank, 1024, 512, 1, align=512)
+    vec, spec, _ = vdist.build_stft_slab(eng, rows, plan, normalize, None, fs=56e6)
+    return plan, rows, vec, spec
+
+
+@pytest.mark.parametrize("name", ["wf_2p5ms_shift_norm", "overlap_5ms", "empty_0p5ms", "cfg1_100ms"])
+def test_fused_build_stft_matches_oracle(eng, name):
+    """One kernel for placement + scale + STFT: the vector is bit-identical to the two-pass build,
+    the spectrogram meets the oracle bar and is bit-identical to the stand-alone STFT kernel."""
+    import vector_b200 as vb
+    r = _build(name, eng)
+    case = r["case"]
+    plan, rows, vec, spec = _fused(eng, case["configs"], r["packets"], r["n"], case["normalize"])
+    assert torch.equal(vec, r["dev"])
+    if r["n"] < 1024:
+        assert spec.shape[1] == 0
+        return
+    fr, tr, Sr = O.full_rate_spectrogram(r["want"], 56e6)
+    S = spec.cpu().numpy()
+    if not np.any(r["want"]):
+        assert S.shape == Sr.shape and not np.any(S)
+        return
+    _, _, St = O.stft_psd_f64(r["want"], 56e6, "hann", 1024, 512, 1024, "density")
+    _check_spec(S, Sr, St)
+    _, _, S2 = vb.full_rate_spectrogram_device(r["dev"], 56e6, engine=eng)
+    assert torch.equal(spec, S2)
+
+
+@pytest.mark.parametrize("n", [1023, 1024, 1025, 8192, 8193, 8704, 8705, 16 * 512 * 3 + 511, 300_001])
+def test_fused_ragged_lengths(eng, n):
+    """Tile edges: vectors shorter than a frame, exactly one tile, odd tails, partial last tiles."""
+    import vector_b200 as vb
+    from vector_b200 import generate
+    cfgs = O._rows_to_configs([("noise", 0.5, 0.01, 0.003), ("multitone", -2, 0.4, 0.0), ("bpsk", 1, 0.13, 0.05)])
+    for c in cfgs:
+        c["period"] = max(c["period"], 1e-5)
+    pk = [(y[:700], pre) for y, pre in O.packets_for(cfgs)]          # short packets so that they fit
+    want = O.build_vector(pk, cfgs, n, True)[0]
+    plan, rows, vec, spec = _fused(eng, cfgs, pk, n, True)
+    ref, _, _, _ = generate.build_vector_device(cfgs, n, True, packets=pk, engine=eng)
+    assert vec.numel() == n and torch.equal(vec, ref)
+    assert P.rel_l2(vec.cpu().numpy(), want) <= 3e-7
+    nf = 0 if n < 1024 else (n - 1024) // 512 + 1
+    assert spec.shape == (1024, nf)
+    if nf:
+        _, _, S2 = vb.full_rate_spectrogram_device(ref, 56e6, engine=eng)
+        assert torch.equal(spec, S2)
+        _, _, Sr = O.full_rate_spectrogram(want, 56e6)
+        assert P.spec_db_error(spec.cpu().numpy(), Sr) <= P.SPEC_DB
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_fused_slabs_concatenate(eng, world):
+    """Time-slab sharding of the fused step, ranks emulated one after another on one GPU: slabs and
+    spectrogram columns concatenate to the single-GPU result bit for bit."""
+    from vector_b200 import dist as vdist, generate
+    from vector_b200._lib import BUILD_MAXONLY, BUILD_SCALE
+    case = cases.build_cases()["cfg1_100ms"]
+    cfgs, n = case["configs"], 5_600_000 + 300                         # not a multiple of 512
+    pk = O.packets_for(cfgs)
+    plan1, rows, vec1, spec1 = _fused(eng, cfgs, pk, n, True)
+    descs, nd = eng.make_descs(rows)
+    plans = [vdist.plan_slab(n, world, r, 1024, 512, 1, align=512) for r in range(world)]
+    assert plans[0].lo == 0 and plans[-1].hi == n and plans[-1].frame_hi == plan1.frame_hi
+    maxsq = torch.zeros(1, dtype=torch.float64, device=eng.device)
+    for pl in plans:                                                  # pass A per rank, MAX-combined
+        m = torch.zeros(1, dtype=torch.float64, device=eng.device)
+        eng.build_pass(descs, nd, pl.lo, pl.hi, None, BUILD_MAXONLY, maxsq=m)
+        maxsq = torch.maximum(maxsq, m)
+    vecs, specs = [], []
+    for pl in plans:
+        v = torch.empty(pl.hi - pl.lo, dtype=torch.complex64, device=eng.device)
+        sp = eng.alloc_spectrogram(1024, pl.frame_hi - pl.frame_lo)
+        eng.build_stft1024(descs, nd, pl.lo, pl.hi, v, BUILD_SCALE, pl.frame_lo, pl.frame_hi - pl.frame_lo, sp,
+                           fs=56e6, maxsq=maxsq)
+        vecs.append(v); specs.append(sp)
+    assert torch.equal(torch.cat(vecs), vec1)
+    assert torch.equal(torch.cat(specs, dim=1), spec1)
+
+
+@pytest.mark.slow
+def test_fused_full_size(eng):
+    """BASELINE size (56 M samples, 109 374 frames): fused == two-pass build + stand-alone STFT."""
+    import vector_b200 as vb
+    from vector_b200 import generate
+    cfgs = O.cfg2_configs()
+    pk = O.packets_for(cfgs)
+    n = 56_000_000
+    plan, rows, vec, spec = _fused(eng, cfgs, pk, n, True)
+    ref, _, counts, _ = generate.build_vector_device(cfgs, n, True, packets=pk, engine=eng)
+    assert counts == [10, 20, 49, 97, 192, 475]
+    assert torch.equal(vec, ref)
+    _, _, S2 = vb.full_rate_spectrogram_device(ref, 56e6, engine=eng)
+    assert spec.shape == (1024, 109_374) and torch.equal(spec, S2)
+    # Parseval per frame: sum_k |X_k|^2 * scale == sum_n |w_n x_n|^2 * 1024 * scale
+    w = torch.from_numpy(scipy.signal.get_window("hann", 1024)).to(eng.device)
+    scale = 1.0 / (56e6 * float((w * w).sum()))
+    for f in (0, 1, 54_321, 109_373):
+        seg = ref[f * 512: f * 512 + 1024].to(torch.complex128) * w
+        want = float((seg.abs() ** 2).sum()) * 1024 * scale
+        got = float(spec[:, f].double().sum())
+        assert abs(got - want) <= 1e-5 * max(want, 1e-30)
+    del vec, spec, ref, S2
+
+
 @pytest.mark.parametrize("name", ["wf_2p5ms_shift_norm", "overlap_5ms", "cfg1_100ms"])
 def test_create_spectrogram_matches_oracle_and_reference(eng, name, golden_meta, golden_arrays):
     import vector_b200 as vb

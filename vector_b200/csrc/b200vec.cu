@@ -5,6 +5,7 @@
 #include "place.cuh"
 #include "stft.cuh"
 #include "stft1024.cuh"
+#include "fused1024.cuh"
 #include "select.cuh"
 
 namespace b200vec {
@@ -93,7 +94,7 @@ int b200vec_create(int device, b200vec_ctx **out) {
                                  B200VEC_MAX_RANKS * kBins3 * 4));
     B2_CUDA(cudaFuncSetAttribute(stft_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  200 * 1024));
-    if (stft1024_setup()) { delete ctx; return 1; }
+    if (stft1024_setup() || fused1024_setup()) { delete ctx; return 1; }
     *out = ctx;
     return 0;
 }
@@ -265,6 +266,66 @@ int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_
     const long long grid = (n_frames + a.T - 1) / a.T;
     B2_REQUIRE(grid < (1LL << 31), "too many frames for one launch");
     stft_generic_kernel<<<(unsigned)grid, kStftThreads, smem, st>>>(a);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+static int fill_place_args(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                           int64_t slab_lo, int64_t slab_hi, PlaceArgs &args) {
+    memset(&args, 0, sizeof(args));
+    args.lo = slab_lo; args.hi = slab_hi;
+    int np = 0;
+    for (int i = 0; i < n_pkts; ++i) {
+        const b200vec_pkt_desc &d = descs[i];
+        B2_REQUIRE(d.slot >= 0 && d.slot < B200VEC_MAX_SLOTS, "descriptor slot out of range");
+        const BankSlot &sl = ctx->slots[d.slot];
+        B2_REQUIRE(sl.len > 0, "descriptor names an uncommitted bank slot");
+        B2_REQUIRE(d.period > 0, "period must be positive");
+        B2_REQUIRE(d.start >= 0 && d.count >= 0, "negative start/count");
+        if (d.count == 0) continue;
+        PlaceDesc &p = args.d[np++];
+        p.start = d.start; p.period = d.period; p.count = d.count;
+        p.len = (int)sl.len; p.a = sl.a; p.b = sl.b;
+    }
+    args.np = np;
+    return 0;
+}
+
+int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                           int64_t slab_lo, int64_t slab_hi, void *vec_out_dev, int mode,
+                           double *maxsq_dev, const float *window_dev, float scale,
+                           int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                           int *nonzero_flag_dev, void *stream) {
+    B2_REQUIRE(ctx, "ctx is NULL");
+    B2_REQUIRE(n_pkts >= 0 && n_pkts <= B200VEC_MAX_PACKETS, "too many packets");
+    B2_REQUIRE(n_pkts == 0 || descs, "descs is NULL");
+    B2_REQUIRE(slab_lo >= 0 && slab_hi >= slab_lo, "bad slab");
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || mode == B200VEC_BUILD_SCALE, "mode must be STORE or SCALE");
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || maxsq_dev, "maxsq_dev is NULL");
+    B2_REQUIRE(vec_out_dev || slab_hi == slab_lo, "vec_out_dev is NULL");
+    B2_REQUIRE(((uintptr_t)vec_out_dev & 15) == 0, "vec_out_dev must be 16-byte aligned");
+    B2_REQUIRE(window_dev && (spec_out_dev || n_frames == 0), "NULL argument");
+    B2_REQUIRE(frame_lo >= 0 && n_frames >= 0 && out_ld >= n_frames, "bad geometry");
+    B2_REQUIRE(out_ld < (1LL << 24), "out_ld must be below 2^24 frames per launch (split the slab)");
+    B2_REQUIRE(slab_lo == frame_lo * kFMaxHop, "slab_lo must equal frame_lo * 512 (slabs are cut on hop boundaries)");
+    B2_REQUIRE(n_frames * kFMaxHop <= slab_hi - slab_lo + kFMaxHop - 1, "frames must start inside the slab");
+    FArgs a;
+    if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place)) return 1;
+    const long long t_frames = (n_frames + kFWarps - 1) / kFWarps;
+    const long long t_vec = (slab_hi - slab_lo + kFOwn - 1) / kFOwn;
+    a.n_tiles = t_frames > t_vec ? t_frames : t_vec;
+    if (a.n_tiles == 0) return 0;
+    a.vec = (float2 *)vec_out_dev;
+    a.maxsq = reinterpret_cast<const unsigned long long *>(maxsq_dev);
+    a.mode = mode; a.hop = kFMaxHop; a.in_origin = slab_lo;
+    a.window = window_dev; a.scale = scale;
+    a.frame_lo = frame_lo; a.n_frames = n_frames; a.out = spec_out_dev; a.out_ld = out_ld;
+    a.flag = nonzero_flag_dev;
+    DeviceGuard g(ctx->device);
+    if (get_tw1024(ctx, &a.tw)) return 1;
+    const long long grid = a.n_tiles < ctx->sm_count ? a.n_tiles : ctx->sm_count;
+    tile1024_kernel<true><<<(unsigned)grid, kFThreads, kFSmem, (cudaStream_t)stream>>>(a);
     B2_CUDA(cudaGetLastError());
     return 0;
 }

@@ -361,6 +361,8 @@ inline int get_tw1024(b200vec_ctx *ctx, const float2 **out) {
     return 0;
 }
 
+int launch_tile1024_plain(b200vec_ctx *ctx, const S1Args &a, cudaStream_t st);   // fused1024.cuh
+
 inline int launch_stft1024(b200vec_ctx *ctx, const float2 *in, long long in_origin, long long in_len,
                            long long stride, int nperseg, int hop, const float *window, float scale,
                            long long frame_lo, long long n_frames, float *out, long long out_ld,
@@ -377,8 +379,10 @@ inline int launch_stft1024(b200vec_ctx *ctx, const float2 *in, long long in_orig
     const bool tma_ok = stride == 1 && nperseg == 1024 && hop <= 512 && (hop & 1) == 0 &&
                         ((reinterpret_cast<uintptr_t>(in + first)) & 15) == 0 && !(no_tma && no_tma[0] == '0');
     if (tma_ok) {
-        const char *wsel = getenv("B200VEC_STFT_W");           // "8": two 8-warp CTAs per SM (A/B tests); default one 16-warp CTA
-        if (wsel && wsel[0] == '8') {
+        const char *wsel = getenv("B200VEC_STFT_W");           // "8"/"16": the v2 tile-transposing kernels (A/B tests)
+        if (!wsel && out_ld < (1LL << 24)) {                   // default: direct-store kernel (fused1024.cuh)
+            return launch_tile1024_plain(ctx, a, st);
+        } else if (wsel[0] == '8') {
             const long long nt = (n_frames + 7) / 8;
             long long grid = nt < 2LL * ctx->sm_count ? nt : 2LL * ctx->sm_count;
             stft1024_tma_kernel<8><<<(unsigned)grid, 256, T1<8>::kSmem, st>>>(a);

@@ -76,3 +76,34 @@ def stft_slab(engine, vec, plan, window="hann", nperseg=1024, noverlap=512, nfft
     return engine.stft(vec, window, nperseg, noverlap, nfft, fs, scaling=scaling, stride=stride,
                        in_origin=plan.lo, frame_lo=plan.frame_lo,
                        n_frames=plan.frame_hi - plan.frame_lo, total_len=plan.total, out=out)
+
+
+def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6, window="hann",
+                    scaling="density", out_vec=None, out_spec=None):
+    """Owned slab of the vector AND this rank's spectrogram columns (hann-1024/512 analysis STFT of
+    vector_analyzer/spectrogram_analysis.py:35-49) with the fused kernel: pass A (max, no stores)
+    -> [all-reduce MAX] -> one kernel that places, scales, stores the vector and transforms it
+    out of shared memory.  `plan` must be cut on hop boundaries: plan_slab(..., align=512).
+    Returns (vector [hi - lo], spectrogram [1024, frame_hi - frame_lo], maxsq or None)."""
+    import torch
+    from ._lib import BUILD_MAXONLY, BUILD_SCALE, BUILD_STORE
+    nf = plan.frame_hi - plan.frame_lo
+    frame_lo = plan.frame_lo if nf > 0 else plan.lo // 512          # a slab past the last frame has none
+    if plan.lo != frame_lo * 512:
+        raise ValueError("build_stft_slab needs slabs cut on hop boundaries: plan_slab(..., align=512)")
+    n = plan.hi - plan.lo
+    if out_vec is None:
+        out_vec = torch.empty(max(n, 0), dtype=torch.complex64, device=engine.device)
+    if out_spec is None:
+        out_spec = engine.alloc_spectrogram(1024, nf)
+    descs, nd = engine.make_descs(rows)
+    mode = BUILD_STORE
+    if normalize:
+        engine._maxsq.zero_()
+        engine.build_pass(descs, nd, plan.lo, plan.hi, None, BUILD_MAXONLY)
+        if reduce_max is not None:
+            reduce_max(engine._maxsq)
+        mode = BUILD_SCALE
+    engine.build_stft1024(descs, nd, plan.lo, plan.hi, out_vec, mode, frame_lo, nf, out_spec,
+                          window=window, fs=fs, scaling=scaling)
+    return out_vec, out_spec, (engine._maxsq if normalize else None)

@@ -123,6 +123,19 @@ class Engine:
         self.build_pass(descs, nd, lo, hi, out, BUILD_SCALE)
         return out, self._maxsq
 
+    def build_stft1024(self, descs, n_descs, lo, hi, vec_out, mode, frame_lo, n_frames, spec_out,
+                       window="hann", fs=H.TARGET_SAMPLE_RATE, scaling="density", maxsq=None, flag=None):
+        """Fused pass B + full-rate STFT (nperseg = nfft = 1024, hop 512): samples [lo, hi) of the
+        vector into vec_out, frames [frame_lo, frame_lo+n_frames) into spec_out, one kernel, the
+        vector never re-read.  lo must equal frame_lo*512."""
+        maxsq = self._maxsq if maxsq is None else maxsq
+        taps, scale = self.window(window, 1024, fs, scaling)
+        check(self.lib.b200vec_build_stft1024(
+            self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), mode, self._ptr(maxsq),
+            self._ptr(taps), scale, int(frame_lo), int(n_frames), self._ptr(spec_out),
+            spec_out.stride(0), self._ptr(flag) if flag is not None else None, self._stream()))
+        self.launches += 1
+
     # ------------------------------------------------------------------ spectrogram
     def window(self, name, nperseg, fs, scaling):
         key = (name, nperseg, float(fs), scaling)
