@@ -2,9 +2,9 @@
 # ncu evidence for the bench step: launch list + full capture of the hot kernels.
 mkdir -p gpurun_out
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu"
-KREGEX="${KREGEX:-stft1024|place_kernel}"
+KREGEX="${KREGEX:-tile1024|place_kernel}"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 $CMD > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:"$KREGEX" -s 9 -c 3 -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"$KREGEX" -s 6 -c 2 -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
 ls -la gpurun_out | head; tail -2 gpurun_out/ncu_full.log

@@ -110,6 +110,7 @@ int b200vec_destroy(b200vec_ctx *ctx) {
     for (auto &kv : ctx->twiddles) cudaFree(kv.second);
     for (auto &s : ctx->fft64) if (s.ptr) cudaFree(s.ptr);
     if (ctx->hist) cudaFree(ctx->hist);
+    if (ctx->zeros) cudaFree(ctx->zeros);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     delete ctx;
     return 0;
@@ -162,12 +163,14 @@ int b200vec_bank_shift(b200vec_ctx *ctx, int slot, double freq_hz, double fs_hz,
         if (sl.store) cudaFree(sl.store);
         sl.store = nullptr; sl.cap_store = 0;
         // per copy: pad | samples (rounded up to even) | pad (+1 spare for the 8-byte phase of copy B)
+        // then the same two copies again, pre-scaled by 1/max (filled per build by bank_scale_kernel)
         const int64_t per = ((len + 1) & ~1LL) + 2 * kBankPad + 2;
-        B2_CUDA(cudaMalloc(&sl.store, (size_t)(2 * per) * sizeof(float2)));
+        B2_CUDA(cudaMalloc(&sl.store, (size_t)(4 * per) * sizeof(float2)));
         sl.cap_store = len;
     }
     const int64_t per = ((sl.cap_store + 1) & ~1LL) + 2 * kBankPad + 2;
-    B2_CUDA(cudaMemsetAsync(sl.store, 0, (size_t)(2 * per) * sizeof(float2), st));
+    B2_CUDA(cudaMemsetAsync(sl.store, 0, (size_t)(4 * per) * sizeof(float2), st));
+    sl.per = per;
     sl.a = sl.store + kBankPad;                 // cudaMalloc is 256-byte aligned, kBankPad is even -> 16-byte aligned
     sl.b = sl.store + per + kBankPad + 1;       // per is even -> 8 mod 16
     // the reference forms the phase as ((2j*pi)*f)*t: w = fl(fl(2*pi)*f)   (utils.py:126)
@@ -272,7 +275,7 @@ int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_
 
 // ---------------------------------------------------------------------------------------
 static int fill_place_args(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
-                           int64_t slab_lo, int64_t slab_hi, PlaceArgs &args) {
+                           int64_t slab_lo, int64_t slab_hi, PlaceArgs &args, int *slot_of = nullptr) {
     memset(&args, 0, sizeof(args));
     args.lo = slab_lo; args.hi = slab_hi;
     int np = 0;
@@ -284,6 +287,7 @@ static int fill_place_args(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
         B2_REQUIRE(d.period > 0, "period must be positive");
         B2_REQUIRE(d.start >= 0 && d.count >= 0, "negative start/count");
         if (d.count == 0) continue;
+        if (slot_of) slot_of[np] = d.slot;
         PlaceDesc &p = args.d[np++];
         p.start = d.start; p.period = d.period; p.count = d.count;
         p.len = (int)sl.len; p.a = sl.a; p.b = sl.b;
@@ -311,23 +315,38 @@ int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
     B2_REQUIRE(slab_lo == frame_lo * kFMaxHop, "slab_lo must equal frame_lo * 512 (slabs are cut on hop boundaries)");
     B2_REQUIRE(n_frames * kFMaxHop <= slab_hi - slab_lo + kFMaxHop - 1, "frames must start inside the slab");
     FArgs a;
-    if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place)) return 1;
-    const long long t_frames = (n_frames + kFWarps - 1) / kFWarps;
-    const long long t_vec = (slab_hi - slab_lo + kFOwn - 1) / kFOwn;
-    a.n_tiles = t_frames > t_vec ? t_frames : t_vec;
-    if (a.n_tiles == 0) return 0;
+    int slot_of[B200VEC_MAX_PACKETS];
+    if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place, slot_of)) return 1;
+    DeviceGuard g(ctx->device);
+    if (!ctx->zeros) {                                     // TMA source for the uncovered part of a span
+        B2_CUDA(cudaMalloc(&ctx->zeros, FL<16>::kSpan * sizeof(float2)));
+        B2_CUDA(cudaMemsetAsync(ctx->zeros, 0, FL<16>::kSpan * sizeof(float2), (cudaStream_t)stream));
+    }
+    a.zeros = ctx->zeros;
+    for (int p = 0; p < B200VEC_MAX_PACKETS; ++p) a.soff[p] = 0;
+    if (mode == B200VEC_BUILD_SCALE && a.place.np > 0) {   // pre-scaled bank copies: fl(y * fl(1 / max))
+        BankScaleArgs sa;
+        memset(&sa, 0, sizeof(sa));
+        for (int p = 0; p < a.place.np; ++p) {
+            BankSlot &sl = ctx->slots[slot_of[p]];
+            a.soff[p] = 2 * sl.per;
+            bool seen = false;
+            for (int q = 0; q < p; ++q) seen = seen || slot_of[q] == slot_of[p];
+            if (seen) continue;
+            sa.store[sa.n] = sl.store; sa.count[sa.n] = 2 * sl.per; ++sa.n;
+        }
+        sa.maxsq = reinterpret_cast<const unsigned long long *>(maxsq_dev);
+        bank_scale_kernel<<<dim3(64, sa.n), 256, 0, (cudaStream_t)stream>>>(sa);
+        B2_CUDA(cudaGetLastError());
+    }
     a.vec = (float2 *)vec_out_dev;
     a.maxsq = reinterpret_cast<const unsigned long long *>(maxsq_dev);
     a.mode = mode; a.hop = kFMaxHop; a.in_origin = slab_lo;
     a.window = window_dev; a.scale = scale;
     a.frame_lo = frame_lo; a.n_frames = n_frames; a.out = spec_out_dev; a.out_ld = out_ld;
     a.flag = nonzero_flag_dev;
-    DeviceGuard g(ctx->device);
     if (get_tw1024(ctx, &a.tw)) return 1;
-    const long long grid = a.n_tiles < ctx->sm_count ? a.n_tiles : ctx->sm_count;
-    tile1024_kernel<true><<<(unsigned)grid, kFThreads, kFSmem, (cudaStream_t)stream>>>(a);
-    B2_CUDA(cudaGetLastError());
-    return 0;
+    return launch_tile1024<true>(ctx, a, n_frames, slab_hi - slab_lo, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -49,6 +49,7 @@ struct BankSlot {
     float2 *a = nullptr;        // -> y[0] of copy A (16-byte aligned)
     float2 *b = nullptr;        // -> y[0] of copy B (8 mod 16)
     int64_t len = 0;            // committed length (0 = not committed)
+    int64_t per = 0;            // samples per copy incl. pads; the pre-scaled copies live 2 * per after the raw ones
 };
 
 struct Scratch {
@@ -65,5 +66,6 @@ struct b200vec_ctx {
     b200vec::Scratch fft64[4];            // fp64 work buffers for the Bluestein resampler
     unsigned int *hist = nullptr;         // select scratch (see select.cuh)
     void *pinned = nullptr;               // small pinned staging block
+    float2 *zeros = nullptr;              // one span of zero samples (bulk-copy source, fused1024.cuh)
     int sm_count = b200vec::kSmCount;
 };

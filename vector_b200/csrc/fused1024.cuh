@@ -31,30 +31,41 @@
 
 namespace b200vec {
 
-constexpr int kFWarps = 16;
-constexpr int kFThreads = 32 * kFWarps;
 constexpr int kFMaxHop = 512;
-constexpr int kFSpan = (kFWarps - 1) * kFMaxHop + 1024;          // 8704 samples per tile at hop 512
-constexpr int kFOwn = kFWarps * kFMaxHop;                        // 8192 samples stored per tile (FUSED)
-constexpr int kFVec = (kFSpan / 2 + kFThreads - 1) / kFThreads;  // 9 float4 per thread (last one half-populated)
 constexpr int kExPitch = 1026;                                   // float2 per frame in the exchange buffer
-constexpr size_t kFOffStage = 0;
-constexpr size_t kFOffExch = kFOffStage + (size_t)kFSpan * sizeof(float2);                 // 69 632
-constexpr size_t kFOffTw = kFOffExch + (size_t)kFWarps * kExPitch * sizeof(float2);       // +131 328
-constexpr size_t kFOffMisc = kFOffTw + 1024 * sizeof(float2);                             // +8 192
-constexpr size_t kFSmem = kFOffMisc + 512;                                                 // 209 664 B
 
-struct FMisc {                       // lives at kFOffMisc
+// Shared-memory plan for W warps = W frames per tile.  W = 16: one 512-thread CTA per SM
+// (209 664 B); W = 8: two 256-thread CTAs per SM (111 232 B each) whose phases interleave.
+template <int W>
+struct FL {
+    static constexpr int kWarps = W;
+    static constexpr int kThreads = 32 * W;
+    static constexpr int kSpan = (W - 1) * kFMaxHop + 1024;          // samples per tile at hop 512
+    static constexpr int kOwn = W * kFMaxHop;                        // samples stored per tile (FUSED)
+    static constexpr int kVec = (kSpan / 2 + kThreads - 1) / kThreads;   // float4 per thread (9)
+    static constexpr int kLastLive = kSpan / 2 - (kVec - 1) * kThreads;  // threads populated in the last round
+    static constexpr int kQPerWarp = 32 / W;                         // P5: q values per warp
+    static constexpr size_t kOffStage = 0;
+    static constexpr size_t kOffExch = kOffStage + (size_t)kSpan * sizeof(float2);
+    static constexpr size_t kOffTw = kOffExch + (size_t)W * kExPitch * sizeof(float2);
+    static constexpr size_t kOffMisc = kOffTw + 1024 * sizeof(float2);
+    static constexpr size_t kSmem = kOffMisc + 512;
+};
+constexpr int kFWarpsDefault = 16;
+
+struct FMisc {                       // lives at kOffMisc
     long long rel[B200VEC_MAX_PACKETS];   // packet index of stage sample 0 for the first overlapping instance
     int cnt[B200VEC_MAX_PACKETS];         // overlapping instances (<= 0: none)
-    int any;
-    int pad;
+    int total;                            // overlapping (packet, instance) pairs over the span (saturating)
+    int first;                            // first packet with cnt > 0
     unsigned long long mbar;
 };
 static_assert(sizeof(FMisc) <= 512, "FMisc must fit its smem slot");
 
 struct FArgs {
     PlaceArgs place;             // FUSED: descriptors + the vector slab [lo, hi) this launch STORES
+    long long soff[B200VEC_MAX_PACKETS];   // FUSED: sample offset from a packet's raw bank copies to its pre-scaled copies (0: unscaled build)
+    const float2 *zeros;         // FUSED: >= kSpan zero samples in HBM/L2 (TMA source for the uncovered part of a span)
     float2 *vec;                 // FUSED: vector out, vec[0] = sample place.lo.  PLAIN: vector in, vec[0] = sample in_origin
     const unsigned long long *maxsq;
     int mode;                    // FUSED: B200VEC_BUILD_STORE or B200VEC_BUILD_SCALE
@@ -68,53 +79,110 @@ struct FArgs {
     long long out_ld;
     int *flag;
     long long n_tiles;
+    int dbg;                     // B200VEC_FUSED_V bit mask, timing experiments only
 };
 
+// Pre-scaled bank copies for a normalised build: scaled[i] = fl(raw[i] * fl(1 / fl(sqrt(maxsq)))),
+// pads included (0 * r = 0).  One launch for every distinct slot a build references.
+struct BankScaleArgs {
+    float2 *store[B200VEC_MAX_PACKETS];     // raw copies A|B; scaled copies follow at + count
+    long long count[B200VEC_MAX_PACKETS];   // samples in the raw pair (2 * per)
+    int n;
+    const unsigned long long *maxsq;
+};
+__global__ void __launch_bounds__(256)
+bank_scale_kernel(const __grid_constant__ BankScaleArgs sa) {
+    const double m2 = __longlong_as_double((long long)*sa.maxsq);
+    const float scl = m2 > 0.0 ? 1.0f / (float)sqrt(m2) : 1.0f;
+    const float4 *src = reinterpret_cast<const float4 *>(sa.store[blockIdx.y]);
+    const long long n4 = sa.count[blockIdx.y] / 2;        // per is even: whole float4s
+    float4 *dst = reinterpret_cast<float4 *>(sa.store[blockIdx.y] + sa.count[blockIdx.y]);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        float4 v = src[i];
+        v.x *= scl; v.y *= scl; v.z *= scl; v.w *= scl;
+        dst[i] = v;
+    }
+}
+
 // P1: instance ranges of every packet over the span of tile t (warp 0, one lane per packet)
+template <int W>
 __device__ __forceinline__ void f_setup_tile(const FArgs &a, long long t, int lane, FMisc *m) {
-    const long long s0 = (a.frame_lo + kFWarps * t) * kFMaxHop;
-    bool has = false;
+    const long long s0 = (a.frame_lo + W * t) * kFMaxHop;
+    int c32 = 0;
     if (lane < a.place.np) {
         const PlaceDesc &d = a.place.d[lane];
         long long klo = floor_div(s0 - d.len - d.start, d.period) + 1;
-        long long khi = floor_div(s0 + kFSpan - 1 - d.start, d.period);
+        long long khi = floor_div(s0 + FL<W>::kSpan - 1 - d.start, d.period);
         if (klo < 0) klo = 0;
         if (khi > d.count - 1) khi = d.count - 1;
         const long long c = khi - klo + 1;
-        m->cnt[lane] = c > 0 ? (int)(c < 0x7fffffff ? c : 0x7fffffff) : 0;
+        c32 = c > 0 ? (int)(c < 0x00ffffff ? c : 0x00ffffff) : 0;
+        m->cnt[lane] = c32;
         m->rel[lane] = s0 - (d.start + klo * d.period);
-        has = c > 0;
     }
-    const unsigned anyb = __ballot_sync(0xffffffffu, has);
-    if (lane == 0) m->any = anyb != 0;
+    const unsigned anyb = __ballot_sync(0xffffffffu, c32 > 0);
+    const int total = __reduce_add_sync(0xffffffffu, c32);
+    if (lane == 0) { m->total = total; m->first = anyb ? __ffs(anyb) - 1 : 0; }
 }
 
-template <bool FUSED>
+__device__ __forceinline__ void tma_bulk_g2s_chunked(unsigned dst, const char *src, unsigned bytes, unsigned mbar) {
+    for (unsigned off = 0; off < bytes; off += 16384) {
+        const unsigned n = (bytes - off < 16384u) ? (bytes - off) : 16384u;
+        tma_bulk_g2s(dst + off, src + off, n, mbar);
+    }
+}
+__device__ __forceinline__ void tma_bulk_s2g(void *dst, unsigned src, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+
+// PLAIN: the span of tile t arrives from the vector in HBM.
+template <int W>
 __device__ __forceinline__ void f_issue_tma(const FArgs &a, long long t, unsigned stage_u32, unsigned mbar) {
-    const long long f0 = t * kFWarps;
-    const int nfr = (int)((a.n_frames - f0 < kFWarps) ? (a.n_frames - f0) : kFWarps);
+    const long long f0 = t * W;
+    const int nfr = (int)((a.n_frames - f0 < W) ? (a.n_frames - f0) : W);
     const unsigned bytes = (unsigned)(((nfr - 1) * a.hop + 1024) * sizeof(float2));
     const char *src = reinterpret_cast<const char *>(a.vec + ((a.frame_lo + f0) * a.hop - a.in_origin));
     mbar_expect_tx(mbar, bytes);
-    for (unsigned off = 0; off < bytes; off += 16384) {
-        const unsigned n = (bytes - off < 16384u) ? (bytes - off) : 16384u;
-        tma_bulk_g2s(stage_u32 + off, src + off, n, mbar);
-    }
+    tma_bulk_g2s_chunked(stage_u32, src, bytes, mbar);
 }
 
-template <bool FUSED>
-__global__ void __launch_bounds__(kFThreads, 1)
+// FUSED, span covered by exactly ONE (packet, instance): the span is that packet's pre-scaled bank
+// copy (fl(y * r), the very value `vector / max` has where nothing else was added) plus zeros, so
+// it is assembled entirely by bulk copies — no registers, no issue slots, one tile ahead.  The
+// piece boundaries are rounded outwards to even samples (16 bytes); the extra sample is one of
+// the bank's zero pads.
+template <int W>
+__device__ __forceinline__ void f_issue_single(const FArgs &a, const FMisc *m, unsigned stage_u32, unsigned mbar) {
+    constexpr int span = FL<W>::kSpan;
+    const int p = m->first;
+    const PlaceDesc &d = a.place.d[p];
+    const int rel = (int)m->rel[p];
+    const int lo = rel < 0 ? ((-rel) & ~1) : 0;
+    const int end = d.len - rel;                                   // > 0
+    const int hi = end >= span ? span : ((end + 1) & ~1);
+    const float2 *base = ((rel & 1) ? d.b : d.a) + a.soff[p] + rel;   // base + even s is 16-byte aligned
+    mbar_expect_tx(mbar, (unsigned)(span * sizeof(float2)));
+    if (lo > 0) tma_bulk_g2s_chunked(stage_u32, reinterpret_cast<const char *>(a.zeros), (unsigned)lo * 8u, mbar);
+    tma_bulk_g2s_chunked(stage_u32 + (unsigned)lo * 8u, reinterpret_cast<const char *>(base + lo), (unsigned)(hi - lo) * 8u, mbar);
+    if (hi < span) tma_bulk_g2s_chunked(stage_u32 + (unsigned)hi * 8u, reinterpret_cast<const char *>(a.zeros), (unsigned)(span - hi) * 8u, mbar);
+}
+
+template <bool FUSED, int W>
+__global__ void __launch_bounds__(32 * W, 16 / W)
 tile1024_kernel(const __grid_constant__ FArgs a) {
+    using L = FL<W>;
     extern __shared__ __align__(128) unsigned char f_smem[];
-    float2 *stage = reinterpret_cast<float2 *>(f_smem + kFOffStage);
-    float2 *exch = reinterpret_cast<float2 *>(f_smem + kFOffExch);
-    float2 *tw = reinterpret_cast<float2 *>(f_smem + kFOffTw);
-    FMisc *misc = reinterpret_cast<FMisc *>(f_smem + kFOffMisc);
+    float2 *stage = reinterpret_cast<float2 *>(f_smem + L::kOffStage);
+    float2 *exch = reinterpret_cast<float2 *>(f_smem + L::kOffExch);
+    float2 *tw = reinterpret_cast<float2 *>(f_smem + L::kOffTw);
+    FMisc *misc = reinterpret_cast<FMisc *>(f_smem + L::kOffMisc);
     const unsigned stage_u32 = smem_u32(stage);
     const unsigned mbar = smem_u32(&misc->mbar);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < 1024; i += kFThreads) tw[i] = __ldg(a.tw + i);
+    for (int i = tid; i < 1024; i += L::kThreads) tw[i] = __ldg(a.tw + i);
     float wreg[32];                                   // this lane's window taps * sqrt(scale), resident
     {
         const float rs = sqrtf(a.scale);
@@ -128,28 +196,44 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
     }
     const int hop = FUSED ? kFMaxHop : a.hop;
     long long t = blockIdx.x;
+    const bool use_single = FUSED && !(a.dbg & 16);              // bit 16: force the register path (A/B)
+    if (tid == 0) mbar_init(mbar, 1);
     if (FUSED) {
-        if (warp == 0 && t < a.n_tiles) f_setup_tile(a, t, lane, misc);
+        if (warp == 0 && t < a.n_tiles) {
+            f_setup_tile<W>(a, t, lane, misc);
+            __syncwarp();
+            if (lane == 0 && use_single && misc->total == 1 && !(a.dbg & 32)) f_issue_single<W>(a, misc, stage_u32, mbar);
+        }
     } else if (tid == 0) {
-        mbar_init(mbar, 1);
-        if (t < a.n_tiles) f_issue_tma<FUSED>(a, t, stage_u32, mbar);
+        if (t < a.n_tiles) f_issue_tma<W>(a, t, stage_u32, mbar);
     }
     __syncthreads();
 
     unsigned anybits = 0, parity = 0;
-    const int f5 = lane & 15, q5 = 2 * warp + (lane >> 4);      // P5/P6 role of this thread
+    const int f5 = lane & (W - 1), q5 = L::kQPerWarp * warp + lane / W;      // P5/P6 role of this thread
     for (; t < a.n_tiles; t += gridDim.x) {
-        const long long f0 = t * kFWarps;                        // first frame of the tile, relative to frame_lo
-        const int nfr = (int)((a.n_frames - f0 < kFWarps) ? (a.n_frames - f0) : kFWarps);   // may be <= 0 (FUSED tail)
+        const long long f0 = t * W;                        // first frame of the tile, relative to frame_lo
+        const int nfr = (int)((a.n_frames - f0 < W) ? (a.n_frames - f0) : W);   // may be <= 0 (FUSED tail)
         bool live = true;                                        // block-uniform: the tile holds signal
+        bool single = false;                                     // block-uniform: span assembled by bulk copies
+        int rem = 0;
+        float2 *dst = nullptr;
         // ------------------------------------------------------------------ P2
         if (FUSED) {
             const long long s0 = (a.frame_lo + f0) * kFMaxHop;
-            live = misc->any != 0;
-            float4 acc[kFVec];
+            const int total = misc->total;
+            live = total != 0;
+            single = use_single && total == 1;
+            const long long rem64 = a.place.hi - s0;             // samples of this tile inside the slab
+            rem = rem64 > L::kOwn ? L::kOwn : (rem64 < 0 ? 0 : (int)rem64);
+            dst = a.vec + (s0 - a.place.lo);
+            if (single) {                                        // the span was assembled by bulk copies (f_issue_single)
+                if (!(a.dbg & 32)) { mbar_wait(mbar, parity); parity ^= 1; }
+            } else {
+            float4 acc[L::kVec];
 #pragma unroll
-            for (int j = 0; j < kFVec; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (live) {
+            for (int j = 0; j < L::kVec; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (live && !(a.dbg & 32)) {
                 for (int p = 0; p < a.place.np; ++p) {
                     const int cnt = misc->cnt[p];
                     if (cnt <= 0) continue;
@@ -159,21 +243,21 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
                     for (int i = 0; i < cnt; ++i, r64 -= d.period) {
                         const int rel = (int)r64;
                         const float2 *base = ((rel & 1) ? d.b : d.a) + rel;
-                        if (rel >= 0 && rel + kFSpan <= len) {
+                        if (rel >= 0 && rel + L::kSpan <= len) {
 #pragma unroll
-                            for (int j = 0; j < kFVec; ++j) {
-                                if (j == kFVec - 1 && tid >= (kFSpan / 2 - (kFVec - 1) * kFThreads)) break;
-                                const float4 v = __ldg(reinterpret_cast<const float4 *>(base + 2 * (tid + kFThreads * j)));
+                            for (int j = 0; j < L::kVec; ++j) {
+                                if (j == L::kVec - 1 && tid >= (L::kLastLive)) break;
+                                const float4 v = (a.dbg & 8) ? __ldcg(reinterpret_cast<const float4 *>(base + 2 * (tid + L::kThreads * j))) : __ldg(reinterpret_cast<const float4 *>(base + 2 * (tid + L::kThreads * j)));
                                 acc[j].x += v.x; acc[j].y += v.y; acc[j].z += v.z; acc[j].w += v.w;
                             }
                         } else {
 #pragma unroll
-                            for (int j = 0; j < kFVec; ++j) {
-                                if (j == kFVec - 1 && tid >= (kFSpan / 2 - (kFVec - 1) * kFThreads)) break;
-                                const int s = 2 * (tid + kFThreads * j);
+                            for (int j = 0; j < L::kVec; ++j) {
+                                if (j == L::kVec - 1 && tid >= (L::kLastLive)) break;
+                                const int s = 2 * (tid + L::kThreads * j);
                                 const int n = s + rel;
                                 if (n >= -1 && n < len) {        // the bank's zero pads cover n = -1 and n + 1 = len
-                                    const float4 v = __ldg(reinterpret_cast<const float4 *>(base + s));
+                                    const float4 v = (a.dbg & 8) ? __ldcg(reinterpret_cast<const float4 *>(base + s)) : __ldg(reinterpret_cast<const float4 *>(base + s));
                                     acc[j].x += v.x; acc[j].y += v.y; acc[j].z += v.z; acc[j].w += v.w;
                                 }
                             }
@@ -181,29 +265,32 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
                     }
                 }
             }
-            float2 *dst = a.vec + (s0 - a.place.lo);
             float4 *st4 = reinterpret_cast<float4 *>(stage);
-            const long long rem64 = a.place.hi - s0;             // samples of this tile inside the slab
-            const int rem = rem64 > kFOwn ? kFOwn : (rem64 < 0 ? 0 : (int)rem64);
 #pragma unroll
-            for (int j = 0; j < kFVec; ++j) {
-                if (j == kFVec - 1 && tid >= (kFSpan / 2 - (kFVec - 1) * kFThreads)) break;
+            for (int j = 0; j < L::kVec; ++j) {
+                if (j == L::kVec - 1 && tid >= (L::kLastLive)) break;
                 float4 v = acc[j];
                 v.x *= scl; v.y *= scl; v.z *= scl; v.w *= scl;
-                const int s = 2 * (tid + kFThreads * j);
-                if (live) st4[tid + kFThreads * j] = v;
-                if (j < kFVec - 1) {                             // s < kFOwn: this tile owns the sample
+                const int s = 2 * (tid + L::kThreads * j);
+                if (live) st4[tid + L::kThreads * j] = v;
+                if (j < L::kVec - 1 && !(a.dbg & 2)) {             // s < L::kOwn: this tile owns the sample
                     if (s + 1 < rem) __stcs(reinterpret_cast<float4 *>(dst + s), v);
                     else if (s < rem) __stcs(dst + s, make_float2(v.x, v.y));
                 }
+            }
             }
         } else {
             mbar_wait(mbar, parity);
             parity ^= 1;
         }
         __syncthreads();                                          // A: stage full (and last tile's exchange reads done)
+        if (FUSED && single && tid == 0 && rem > 0 && !(a.dbg & 2)) {   // vector store of a bulk-assembled span: smem -> HBM bulk copy
+            if (rem > 1) tma_bulk_s2g(dst, stage_u32, (unsigned)(rem & ~1) * 8u);
+            tma_store_commit();
+            if (rem & 1) __stcs(dst + rem - 1, stage[rem - 1]);
+        }
         // ------------------------------------------------------------------ P3 + P4
-        if (live && warp < nfr) {
+        if (live && warp < nfr && !(a.dbg & 64)) {
             cf32 v[32];
             const float2 *sp = stage + warp * hop + lane;
 #pragma unroll
@@ -211,14 +298,20 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
                 const float2 x = sp[32 * brev5(i)];
                 v[i].x = x.x; v[i].y = x.y;
             }
-            fft32_windowed(v, wreg);
+            if (!(a.dbg & 4)) fft32_windowed(v, wreg);
             float2 *ex = exch + warp * kExPitch + lane;
 #pragma unroll
             for (int q = 0; q < 32; ++q) ex[32 * q] = make_float2(v[q].x, v[q].y);
         }
-        if (FUSED && warp == 0 && t + gridDim.x < a.n_tiles) f_setup_tile(a, t + gridDim.x, lane, misc);   // P1 (next tile)
+        if (FUSED && warp == 0) {
+            if (t + gridDim.x < a.n_tiles) f_setup_tile<W>(a, t + gridDim.x, lane, misc);   // P1 (next tile)
+            if (lane == 0 && single) tma_store_wait_read();      // the vector bulk store has finished reading the stage
+        }
         __syncthreads();                                          // B: exchange full, stage free
-        if (!FUSED && tid == 0 && t + gridDim.x < a.n_tiles) f_issue_tma<FUSED>(a, t + gridDim.x, stage_u32, mbar);
+        if (tid == 0 && t + gridDim.x < a.n_tiles) {
+            if (!FUSED) f_issue_tma<W>(a, t + gridDim.x, stage_u32, mbar);
+            else if (use_single && misc->total == 1 && !(a.dbg & 32)) f_issue_single<W>(a, misc, stage_u32, mbar);
+        }
         // ------------------------------------------------------------------ P5 + P6
         if (f5 < nfr) {
             // row q + 32 sp, sp = 8 hi + lo: four 64-bit row-group bases, 32-bit offsets inside a group
@@ -227,7 +320,7 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
             float *og[4];
 #pragma unroll
             for (int h = 0; h < 4; ++h) og[h] = o + (long long)h * 256 * a.out_ld;
-            if (live) {
+            if (live && !(a.dbg & 64)) {
                 cf32 v[32];
                 const float4 *ex4 = reinterpret_cast<const float4 *>(exch + f5 * kExPitch + q5 * 32);
 #pragma unroll
@@ -237,13 +330,13 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
                     v[brev5(l + 1)].x = x.z; v[brev5(l + 1)].y = x.w;
                 }
                 const float2 *tq = tw + q5 * 32;
-                fft32_twiddled(v, [tq](int l) { const float2 w = tq[l]; return cf32{w.x, w.y}; });
+                if (!(a.dbg & 4)) fft32_twiddled(v, [tq](int l) { const float2 w = tq[l]; return cf32{w.x, w.y}; });
 #pragma unroll
                 for (int sp = 0; sp < 32; ++sp) {                 // output row q + 32 sp holds bin q + 32 s, s = (sp + 16) & 31
                     const int s = (sp + 16) & 31;
                     const float p = b2_fma(v[s].x, v[s].x, v[s].y * v[s].y);
                     anybits |= __float_as_uint(p);                // p >= 0 or NaN: non-zero bits <=> p != 0
-                    __stcs(og[sp >> 3] + (unsigned)(sp & 7) * step, p);
+                    if (!(a.dbg & 1) || p < 0.0f) __stcs(og[sp >> 3] + (unsigned)(sp & 7) * step, p);
                 }
             } else {
 #pragma unroll
@@ -254,6 +347,31 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
     if (a.flag && __syncthreads_or(anybits != 0) && tid == 0) atomicOr(a.flag, 1);
 }
 
+// W = frames per tile: 16 -> one 512-thread CTA per SM, 8 -> two 256-thread CTAs per SM.
+// B200VEC_FUSED_W=8|16 overrides the default (A/B runs, scripts/fused_ab.py).
+inline int fused_w() {
+    const char *e = getenv("B200VEC_FUSED_W");
+    if (e && e[0] == '8') return 8;
+    if (e && e[0] == '1') return 16;
+    return kFWarpsDefault;
+}
+
+template <bool FUSED>
+inline int launch_tile1024(b200vec_ctx *ctx, FArgs &a, long long n_frames, long long n_vec, cudaStream_t st) {
+    const int w = fused_w();
+    { const char *e = getenv("B200VEC_FUSED_V"); a.dbg = e ? atoi(e) : 0; }
+    const long long own = (long long)w * kFMaxHop;
+    const long long t_frames = (n_frames + w - 1) / w, t_vec = (n_vec + own - 1) / own;
+    a.n_tiles = t_frames > t_vec ? t_frames : t_vec;
+    if (a.n_tiles == 0) return 0;
+    const long long cap = (long long)ctx->sm_count * (16 / w);
+    const long long grid = a.n_tiles < cap ? a.n_tiles : cap;
+    if (w == 8) tile1024_kernel<FUSED, 8><<<(unsigned)grid, FL<8>::kThreads, FL<8>::kSmem, st>>>(a);
+    else tile1024_kernel<FUSED, 16><<<(unsigned)grid, FL<16>::kThreads, FL<16>::kSmem, st>>>(a);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
 inline int launch_tile1024_plain(b200vec_ctx *ctx, const S1Args &s, cudaStream_t st) {
     FArgs a;
     memset(&a, 0, sizeof(a));
@@ -261,16 +379,14 @@ inline int launch_tile1024_plain(b200vec_ctx *ctx, const S1Args &s, cudaStream_t
     a.hop = s.hop; a.in_origin = s.in_origin;
     a.window = s.window; a.tw = s.tw; a.scale = s.scale;
     a.frame_lo = s.frame_lo; a.n_frames = s.n_frames; a.out = s.out; a.out_ld = s.out_ld; a.flag = s.flag;
-    a.n_tiles = (s.n_frames + kFWarps - 1) / kFWarps;
-    const long long grid = a.n_tiles < ctx->sm_count ? a.n_tiles : ctx->sm_count;
-    tile1024_kernel<false><<<(unsigned)grid, kFThreads, kFSmem, st>>>(a);
-    B2_CUDA(cudaGetLastError());
-    return 0;
+    return launch_tile1024<false>(ctx, a, s.n_frames, 0, st);
 }
 
 inline int fused1024_setup() {
-    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFSmem));
-    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFSmem));
+    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<true, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<16>::kSmem));
+    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<false, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<16>::kSmem));
+    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<8>::kSmem));
+    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<8>::kSmem));
     return 0;
 }
 
