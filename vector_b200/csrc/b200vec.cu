@@ -6,6 +6,7 @@
 #include "stft.cuh"
 #include "stft1024.cuh"
 #include "fused1024.cuh"
+#include "pipe1024.cuh"
 #include "select.cuh"
 
 namespace b200vec {
@@ -94,7 +95,7 @@ int b200vec_create(int device, b200vec_ctx **out) {
                                  B200VEC_MAX_RANKS * kBins3 * 4));
     B2_CUDA(cudaFuncSetAttribute(stft_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  200 * 1024));
-    if (stft1024_setup() || fused1024_setup()) { delete ctx; return 1; }
+    if (stft1024_setup() || fused1024_setup() || pipe1024_setup()) { delete ctx; return 1; }
     *out = ctx;
     return 0;
 }
@@ -346,6 +347,7 @@ int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
     a.frame_lo = frame_lo; a.n_frames = n_frames; a.out = spec_out_dev; a.out_ld = out_ld;
     a.flag = nonzero_flag_dev;
     if (get_tw1024(ctx, &a.tw)) return 1;
+    if (pipe1024_enabled()) return launch_pipe1024<true>(ctx, a, n_frames, slab_hi - slab_lo, (cudaStream_t)stream);
     return launch_tile1024<true>(ctx, a, n_frames, slab_hi - slab_lo, (cudaStream_t)stream);
 }
 
@@ -405,5 +407,12 @@ int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, int16_t
     B2_CUDA(cudaGetLastError());
     return 0;
 }
+
+#ifdef B2_PIPE_TIMING
+int b200vec_debug_pipe_prof(long long *out_host) {   // timing build only (scripts/pipe_timing.py)
+    cudaDeviceSynchronize();
+    return cudaMemcpyFromSymbol(out_host, b200vec::g_pipe_prof, sizeof(long long) * 160 * 16 * 8) != cudaSuccess;
+}
+#endif
 
 }  // extern "C"

@@ -164,4 +164,37 @@ B2_HD void fft32_twiddled(cf32 (&v)[32], const TW &tw) {
     dit_tail(v);
 }
 
+// Same transform with the twiddles fetched two at a time: tq[P] = (W1024^(q la), W1024^(q lb)) with
+// la = brev5(2 P), lb = brev5(2 P + 1) — the order the first stage consumes them, one 16-byte
+// load per butterfly (table built by get_tw1024_pairs).
+struct cf32x2 {
+    float ax, ay, bx, by;
+};
+template <int P, class TW2>
+B2_HD void tw2_bfly(cf32 (&v)[32], const TW2 &tw2) {
+    constexpr int i = 2 * P;
+    const cf32x2 t = tw2(P);
+    cf32 u;
+    if constexpr (P == 0) {                     // la = 0: twiddle 1
+        u = v[i];
+    } else {
+        u.x = b2_fma(-v[i].y, t.ay, v[i].x * t.ax);
+        u.y = b2_fma(v[i].y, t.ax, v[i].x * t.ay);
+    }
+    const cf32 b = v[i + 1];
+    const float y0x = b2_fma(b.x, t.bx, b2_fma(-b.y, t.by, u.x));
+    const float y0y = b2_fma(b.x, t.by, b2_fma(b.y, t.bx, u.y));
+    v[i + 1].x = b2_fma(2.0f, u.x, -y0x);
+    v[i + 1].y = b2_fma(2.0f, u.y, -y0y);
+    v[i].x = y0x; v[i].y = y0y;
+}
+template <class TW2>
+B2_HD void fft32_twiddled_pairs(cf32 (&v)[32], const TW2 &tw2) {
+    tw2_bfly<0>(v, tw2); tw2_bfly<1>(v, tw2); tw2_bfly<2>(v, tw2); tw2_bfly<3>(v, tw2);
+    tw2_bfly<4>(v, tw2); tw2_bfly<5>(v, tw2); tw2_bfly<6>(v, tw2); tw2_bfly<7>(v, tw2);
+    tw2_bfly<8>(v, tw2); tw2_bfly<9>(v, tw2); tw2_bfly<10>(v, tw2); tw2_bfly<11>(v, tw2);
+    tw2_bfly<12>(v, tw2); tw2_bfly<13>(v, tw2); tw2_bfly<14>(v, tw2); tw2_bfly<15>(v, tw2);
+    dit_tail(v);
+}
+
 }  // namespace b200vec

@@ -372,6 +372,9 @@ inline int launch_tile1024(b200vec_ctx *ctx, FArgs &a, long long n_frames, long 
     return 0;
 }
 
+bool pipe1024_enabled();                                                                   // pipe1024.cuh
+int launch_pipe1024_plain(b200vec_ctx *ctx, FArgs &a, long long n_frames, cudaStream_t st);   // pipe1024.cuh
+
 inline int launch_tile1024_plain(b200vec_ctx *ctx, const S1Args &s, cudaStream_t st) {
     FArgs a;
     memset(&a, 0, sizeof(a));
@@ -379,6 +382,7 @@ inline int launch_tile1024_plain(b200vec_ctx *ctx, const S1Args &s, cudaStream_t
     a.hop = s.hop; a.in_origin = s.in_origin;
     a.window = s.window; a.tw = s.tw; a.scale = s.scale;
     a.frame_lo = s.frame_lo; a.n_frames = s.n_frames; a.out = s.out; a.out_ld = s.out_ld; a.flag = s.flag;
+    if (pipe1024_enabled()) return launch_pipe1024_plain(ctx, a, s.n_frames, st);
     return launch_tile1024<false>(ctx, a, s.n_frames, 0, st);
 }
 
