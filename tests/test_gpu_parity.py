@@ -595,3 +595,29 @@ def test_invalid_arguments_fail_loudly(eng):
     x = torch.zeros(4096, dtype=torch.complex64, device="cuda")
     with pytest.raises(B200VecError):
         eng.stft(x, "hann", 1000, 0, 1000, 1.0)                     # nfft not a power of two
+
+
+# ------------------------------------------------------------------------------ ranged max pass
+@pytest.mark.parametrize("name,n", [("cfg1_100ms", 5_600_000), ("overlap_5ms", 280_000)])
+def test_ranged_max_equals_full_max(eng, name, n):
+    """Pass A over hostmath.max_eval_ranges (one common period + head/tail, split over ranks) gives
+    the same max|v|^2 double as pass A over the whole vector, and the oracle's max."""
+    from vector_b200 import generate
+    from vector_b200._lib import BUILD_MAXONLY
+    case = cases.build_cases()[name]
+    pk = O.packets_for(case["configs"])
+    info = generate.prepare_bank(eng, case["configs"], pk, 56e6)
+    rows = generate.placement_rows(case["configs"], info, n, 56e6)
+    descs, nd = eng.make_descs(rows)
+    full = torch.zeros(1, dtype=torch.float64, device=eng.device)
+    eng.build_pass(descs, nd, 0, n, None, BUILD_MAXONLY, maxsq=full)
+    ranges = eng.max_ranges(rows, n)
+    if name == "cfg1_100ms":
+        assert sum(hi - lo for lo, hi in ranges) < n // 2          # periods 1.0/1.2/1.5 ms: lcm 6 ms
+    for world in (1, 3):
+        m = torch.zeros(1, dtype=torch.float64, device=eng.device)
+        for r in range(world):
+            eng.max_pass(descs, nd, eng.max_ranges(rows, n, world, r), maxsq=m)
+        assert torch.equal(m, full)
+    want = O.build_vector(pk, case["configs"], n, False)[0]
+    assert abs(np.sqrt(full.item()) - float(np.max(np.abs(want)))) <= 2e-7 * np.sqrt(full.item())   # np.abs is a float32 hypot

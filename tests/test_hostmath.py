@@ -184,3 +184,54 @@ def test_product_synth_matches_oracle_synth():
     cfgs, pk = synth.scenario(synth.CFG2_ROWS)
     for (a, pa), (b, pb) in zip(pk, O.packets_for(O.cfg2_configs())):
         assert pa == pb and np.array_equal(a, b)
+
+
+# ------------------------------------------------------------------------------ max-abs ranges
+def _brute_vector(rows, packets, total):
+    """The reference's placement loop (unified_gui.py:1757-1769) in float32, packet then instance order."""
+    v = np.zeros(total, np.complex64)
+    for (start, period, count, _), y in zip(rows, packets):
+        for k in range(count):
+            pos = start + k * period
+            v[pos:pos + len(y)] += y
+    return v
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_max_eval_ranges_give_the_exact_max(seed):
+    """max|v| over hostmath.max_eval_ranges == max|v| over the whole vector, bit for bit, and the
+    claimed period really repeats; random trains incl. self-overlapping ones (L > P)."""
+    rng = np.random.default_rng(seed)
+    total = int(rng.integers(20_000, 60_000))
+    npk = int(rng.integers(1, 5))
+    rows, packets = [], []
+    for p in range(npk):
+        period = int(rng.choice([60, 100, 150, 200, 300, 400, 600]))
+        length = int(rng.integers(10, 2 * period if seed % 3 == 0 else period))
+        start = int(rng.integers(0, 3000))
+        y = (rng.standard_normal(length) + 1j * rng.standard_normal(length)).astype(np.complex64)
+        count = H.instance_count(start, period, length, total)
+        if seed == 5 and p == 0:
+            count = 1 if count else 0                         # a packet placed once: must fall back to the whole vector
+        rows.append((start, period, count, p)); packets.append(y)
+    v = _brute_vector(rows, packets, total)
+    ranges = H.max_eval_ranges(rows, [len(y) for y in packets], total)
+    assert ranges and ranges[0][0] == 0 and all(lo < hi for lo, hi in ranges)
+    assert all(a[1] <= b[0] for a, b in zip(ranges, ranges[1:]))
+    sub = np.concatenate([np.abs(v[lo:hi]) for lo, hi in ranges])
+    assert sub.max() == np.abs(v).max()
+    if seed == 5:
+        assert ranges == [(0, total)]
+    for world in (2, 3):
+        parts = [H.split_ranges(ranges, world, r) for r in range(world)]
+        assert sum(hi - lo for part in parts for lo, hi in part) == sum(hi - lo for lo, hi in ranges)
+        assert max(np.abs(v[lo:hi]).max() for part in parts for lo, hi in part) == np.abs(v).max()
+
+
+def test_max_eval_ranges_cfg2_shape():
+    """BASELINE cfg2: periods 100/50/20/10/5/2 ms -> one 100 ms period + the 49 ms head + the 100-sample tail."""
+    rows = []
+    for per, st in [(100, 0), (50, 10), (20, 20), (10, 30), (5, 40), (2, 50)]:
+        p = H.period_samples(per / 1000, 56e6); s = H.start_offset(st / 1000, 100, 56e6)
+        rows.append((s, p, H.instance_count(s, p, 56100, 56_000_000), 0))
+    assert H.max_eval_ranges(rows, [56100] * 6, 56_000_000) == [(0, 8_344_000), (55_999_900, 56_000_000)]

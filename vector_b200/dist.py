@@ -50,8 +50,9 @@ def make_max_reducer(group=None):
 
 def build_slab(engine, rows, plan, normalize=True, reduce_max=None, out=None):
     """Owned slab plus halo of the (optionally normalised) vector on this rank's GPU.
-    The max is reduced over OWNED samples only (every sample is owned by exactly one rank),
-    the store pass also fills the halo.  Returns (tensor [halo_hi - lo], maxsq or None)."""
+    The max pass covers this rank's share of hostmath.max_eval_ranges (one common period of the
+    packet trains plus the head and tail of the vector — enough for the exact global max), the
+    store pass also fills the halo.  Returns (tensor [halo_hi - lo], maxsq or None)."""
     import torch
     from ._lib import BUILD_MAXONLY, BUILD_SCALE, BUILD_STORE
     n = plan.halo_hi - plan.lo
@@ -62,7 +63,7 @@ def build_slab(engine, rows, plan, normalize=True, reduce_max=None, out=None):
         engine.build_pass(descs, nd, plan.lo, plan.halo_hi, out, BUILD_STORE)
         return out, None
     engine._maxsq.zero_()
-    engine.build_pass(descs, nd, plan.lo, plan.hi, None, BUILD_MAXONLY)
+    engine.max_pass(descs, nd, engine.max_ranges(rows, plan.total, plan.world, plan.rank))
     if reduce_max is not None:
         reduce_max(engine._maxsq)
     engine.build_pass(descs, nd, plan.lo, plan.halo_hi, out, BUILD_SCALE)
@@ -100,7 +101,7 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
     mode = BUILD_STORE
     if normalize:
         engine._maxsq.zero_()
-        engine.build_pass(descs, nd, plan.lo, plan.hi, None, BUILD_MAXONLY)
+        engine.max_pass(descs, nd, engine.max_ranges(rows, plan.total, plan.world, plan.rank))
         if reduce_max is not None:
             reduce_max(engine._maxsq)
         mode = BUILD_SCALE

@@ -102,7 +102,21 @@ class Engine:
                                      self._ptr(maxsq), self._stream()))
         self.launches += 1
 
-    def build_vector(self, rows, total, normalize=True, lo=0, hi=None, out=None, reduce_max=None):
+    def max_ranges(self, rows, total, world=1, rank=0):
+        """This rank's share of the sample ranges whose max|v| is the max over the whole vector
+        (hostmath.max_eval_ranges: periodic trains repeat bit-exactly, so one common period plus
+        the head and tail of the vector is enough)."""
+        rows = list(rows)
+        lengths = [self.bank_len(r[3]) for r in rows]
+        return H.split_ranges(H.max_eval_ranges(rows, lengths, total), world, rank)
+
+    def max_pass(self, descs, n_descs, ranges, maxsq=None):
+        """Pass A: max |v|^2 over the given sample ranges into maxsq (atomic max; zero it first)."""
+        for lo, hi in ranges:
+            self.build_pass(descs, n_descs, lo, hi, None, BUILD_MAXONLY, maxsq=maxsq)
+
+    def build_vector(self, rows, total, normalize=True, lo=0, hi=None, out=None, reduce_max=None,
+                     world=1, rank=0):
         """Samples [lo, hi) of the composite vector as a complex64 CUDA tensor.
 
         normalize=True runs the two-pass recompute: pass A reduces max|v|^2 over the slab
@@ -117,7 +131,10 @@ class Engine:
             self.build_pass(descs, nd, lo, hi, out, BUILD_STORE)
             return out, None
         self._maxsq.zero_()
-        self.build_pass(descs, nd, lo, hi, None, BUILD_MAXONLY)
+        if reduce_max is None and (lo != 0 or hi != total):
+            self.build_pass(descs, nd, lo, hi, None, BUILD_MAXONLY)      # a lone sub-range: its own max
+        else:
+            self.max_pass(descs, nd, self.max_ranges(rows, total, world, rank))
         if reduce_max is not None:
             reduce_max(self._maxsq)
         self.build_pass(descs, nd, lo, hi, out, BUILD_SCALE)

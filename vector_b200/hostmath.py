@@ -406,3 +406,58 @@ def frame_range_for_slab(lo, hi, total, stride, nperseg, hop, n_frames):
         return f_lo, f_lo, hi
     last = ((f_hi - 1) * hop + nperseg - 1) * stride + 1
     return f_lo, f_hi, max(hi, min(total, last))
+
+
+# --------------------------------------------------------------------------- max-abs pass
+def max_eval_ranges(rows, lengths, total):
+    """Sample ranges over which max|v| has to be evaluated to get the max over [0, total).
+
+    The composite is a sum of periodic trains, v(i) = sum_p sum_k y_p[i - s_p - k P_p]
+    (unified_gui.py:1757-1769).  Packet p's train repeats exactly — same y values added in the
+    same (packet, instance) order, hence bit-identical float32 sums — under a shift by its period
+    wherever no instance is entering or leaving:
+        c_p(i + P_p) == c_p(i)   for   max(0, s_p + L_p - P_p) <= i < s_p + (K_p - 1) P_p.
+    With T = lcm(P_p) that gives v(i + T) == v(i) on [A, B),
+        A = max_p max(0, s_p + L_p - P_p),   B = min_p (s_p + K_p P_p - T),
+    so every value taken on [A, B + T) is already taken on [A, A + T) and
+        max over [0, total) = max over [0, A + T) U [B + T, total).
+    Falls back to the whole vector when the trains share no usable period (a packet placed
+    once, T too long, B <= A).  rows: (start, period, count, slot); lengths: packet lengths.
+    Returns a list of disjoint, ascending (lo, hi)."""
+    whole = [(0, int(total))] if total > 0 else []
+    live = [(int(s), int(p), int(k), int(n)) for (s, p, k, _), n in zip(rows, lengths) if k > 0]
+    if not live or total <= 0:
+        return whole
+    if any(k < 2 for _, _, k, _ in live):
+        return whole
+    t = 1
+    for _, p, _, _ in live:
+        t = t * p // math.gcd(t, p)
+        if t >= total:
+            return whole
+    a = max(max(0, s + n - p) for s, p, _, n in live)
+    b = min(s + k * p - t for s, p, k, _ in live)
+    if b <= a or a + t >= b + t or a + t >= total:
+        return whole
+    out = [(0, a + t)]
+    if b + t < total:
+        out.append((b + t, int(total)))
+    return out
+
+
+def split_ranges(ranges, world, rank):
+    """Rank `rank`'s share of a list of sample ranges: the concatenated index space is cut into
+    `world` equal contiguous pieces (any rank can evaluate any sample — placement is a pure
+    function of the descriptors)."""
+    size = sum(hi - lo for lo, hi in ranges)
+    if world <= 1:
+        return list(ranges)
+    c0, c1 = rank * size // world, (rank + 1) * size // world
+    out, pos = [], 0
+    for lo, hi in ranges:
+        n = hi - lo
+        x0, x1 = max(c0, pos), min(c1, pos + n)
+        if x1 > x0:
+            out.append((lo + x0 - pos, lo + x1 - pos))
+        pos += n
+    return out
