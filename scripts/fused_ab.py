@@ -17,7 +17,7 @@ nf = plan.frame_hi - plan.frame_lo
 vec = torch.empty(N, dtype=torch.complex64, device=eng.device)
 spec = eng.alloc_spectrogram(1024, nf)
 descs, nd = eng.make_descs(rows)
-KEYS = ("B200VEC_FUSED_W", "B200VEC_FUSED_V", "B200VEC_PIPE")
+KEYS = ("B200VEC_FUSED_W", "B200VEC_FUSED_V", "B200VEC_PIPE", "B200VEC_FUSED_TS", "B200VEC_FUSED_ZTMA")
 
 
 def run():

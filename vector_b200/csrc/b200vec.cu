@@ -411,7 +411,11 @@ int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, int16_t
 #ifdef B2_PIPE_TIMING
 int b200vec_debug_pipe_prof(long long *out_host) {   // timing build only (scripts/pipe_timing.py)
     cudaDeviceSynchronize();
-    return cudaMemcpyFromSymbol(out_host, b200vec::g_pipe_prof, sizeof(long long) * 160 * 16 * 8) != cudaSuccess;
+    return cudaMemcpyFromSymbol(out_host, b200vec::g_pipe_prof, sizeof(long long) * 320 * 16 * 8) != cudaSuccess;
+}
+int b200vec_debug_pipe_cta(long long *out_host) {
+    cudaDeviceSynchronize();
+    return cudaMemcpyFromSymbol(out_host, b200vec::g_pipe_cta, sizeof(long long) * 320 * 4) != cudaSuccess;
 }
 #endif
 

@@ -24,6 +24,7 @@
 // Two __syncthreads per tile (stage full; exchange full).  HBM traffic: 8 B/sample vector store
 // + 8 B/sample spectrogram store (FUSED), nothing read.
 #pragma once
+#include <cuda.h>
 #include "common.cuh"
 #include "place.cuh"
 #include "fft32.cuh"
@@ -33,6 +34,7 @@ namespace b200vec {
 
 constexpr int kFMaxHop = 512;
 constexpr int kExPitch = 1026;                                   // float2 per frame in the exchange buffer
+constexpr int kTwPitch = 33;                                     // float2 per q row of the twiddle table: adjacent q rows hit different banks
 
 // Shared-memory plan for W warps = W frames per tile.  W = 16: one 512-thread CTA per SM
 // (209 664 B); W = 8: two 256-thread CTAs per SM (111 232 B each) whose phases interleave.
@@ -48,8 +50,11 @@ struct FL {
     static constexpr size_t kOffStage = 0;
     static constexpr size_t kOffExch = kOffStage + (size_t)kSpan * sizeof(float2);
     static constexpr size_t kOffTw = kOffExch + (size_t)W * kExPitch * sizeof(float2);
-    static constexpr size_t kOffMisc = kOffTw + 1024 * sizeof(float2);
-    static constexpr size_t kSmem = kOffMisc + 512;
+    static constexpr size_t kOffWin = kOffTw + 32 * kTwPitch * sizeof(float2);    // window taps * sqrt(scale): [8][32 lanes] float4, in order of use
+    static constexpr size_t kOffMisc = kOffWin + 1024 * sizeof(float);
+    static constexpr size_t kZeroBytes = W == 16 ? 8192 : 0;        // zero source for empty tiles (bulk stores); no room at W = 8
+    static constexpr size_t kOffZero = kOffMisc + 512;
+    static constexpr size_t kSmem = kOffZero + kZeroBytes;
 };
 constexpr int kFWarpsDefault = 16;
 
@@ -63,6 +68,9 @@ struct FMisc {                       // lives at kOffMisc
 static_assert(sizeof(FMisc) <= 512, "FMisc must fit its smem slot");
 
 struct FArgs {
+    alignas(64) CUtensorMap tmap_z; // empty tiles: same tensor, box = W frames x 128 rows (8 KB of zeros at W = 16)
+    int ztma;                       // empty tiles leave by bulk stores from a zeroed shared-memory block (W = 16, tensor map available)
+    alignas(64) CUtensorMap tmap;   // TS kernels: float32 [1024 rows][n_frames], row pitch out_ld, box = W frames x 256 rows
     PlaceArgs place;             // FUSED: descriptors + the vector slab [lo, hi) this launch STORES
     long long soff[B200VEC_MAX_PACKETS];   // FUSED: sample offset from a packet's raw bank copies to its pre-scaled copies (0: unscaled build)
     const float2 *zeros;         // FUSED: >= kSpan zero samples in HBM/L2 (TMA source for the uncovered part of a span)
@@ -169,7 +177,19 @@ __device__ __forceinline__ void f_issue_single(const FArgs &a, const FMisc *m, u
     if (hi < span) tma_bulk_g2s_chunked(stage_u32 + (unsigned)hi * 8u, reinterpret_cast<const char *>(a.zeros), (unsigned)(span - hi) * 8u, mbar);
 }
 
-template <bool FUSED, int W>
+#ifdef B2_PIPE_TIMING
+__device__ long long g_pipe_prof[320][16][8];
+__device__ long long g_pipe_cta[320][4];
+#define PT_DECL long long pt_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}; long long pt_last = clock64(); const long long pt_t0 = pt_last;
+#define PT(k) { const long long pt_now = clock64(); pt_acc[k] += pt_now - pt_last; pt_last = pt_now; }
+#define PT_FLUSH if (lane == 0) { for (int k = 0; k < 8; ++k) g_pipe_prof[blockIdx.x][warp][k] = pt_acc[k]; if (warp == 0) { unsigned sm_; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_)); g_pipe_cta[blockIdx.x][0] = sm_; g_pipe_cta[blockIdx.x][1] = pt_t0; g_pipe_cta[blockIdx.x][2] = clock64(); } }
+#else
+#define PT_DECL
+#define PT(k)
+#define PT_FLUSH
+#endif
+
+template <bool FUSED, int W, bool TS>
 __global__ void __launch_bounds__(32 * W, 16 / W)
 tile1024_kernel(const __grid_constant__ FArgs a) {
     using L = FL<W>;
@@ -182,12 +202,21 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
     const unsigned mbar = smem_u32(&misc->mbar);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < 1024; i += L::kThreads) tw[i] = __ldg(a.tw + i);
-    float wreg[32];                                   // this lane's window taps * sqrt(scale), resident
+    for (int i = tid; i < 1024; i += L::kThreads) tw[(i >> 5) * kTwPitch + (i & 31)] = __ldg(a.tw + i);
+    float4 *win4 = reinterpret_cast<float4 *>(f_smem + L::kOffWin);
+    const bool ztma = FUSED && W == 16 && a.ztma;
+    if (ztma) {
+        float4 *z = reinterpret_cast<float4 *>(f_smem + L::kOffZero);
+        for (int i = tid; i < (int)(L::kZeroBytes / 16); i += L::kThreads) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
     {
         const float rs = sqrtf(a.scale);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) wreg[j] = __ldg(a.window + lane + 32 * j) * rs;
+        float *wf = reinterpret_cast<float *>(win4);
+        for (int i = tid; i < 1024; i += L::kThreads) {     // i = (k * 32 + lane) * 4 + c  ->  tap j = brev5(4 k + c) of lane
+            const int c = i & 3, ln = (i >> 2) & 31, k = i >> 7;
+            wf[i] = __ldg(a.window + ln + 32 * brev5(4 * k + c)) * rs;
+        }
     }
     float scl = 1.0f;
     if (FUSED && a.mode == B200VEC_BUILD_SCALE) {
@@ -196,13 +225,13 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
     }
     const int hop = FUSED ? kFMaxHop : a.hop;
     long long t = blockIdx.x;
-    const bool use_single = FUSED && !(a.dbg & 16);              // bit 16: force the register path (A/B)
+    const bool use_single = FUSED && !(a.dbg & 16);              // B200VEC_FUSED_V=16: force the register path (A/B)
     if (tid == 0) mbar_init(mbar, 1);
     if (FUSED) {
         if (warp == 0 && t < a.n_tiles) {
             f_setup_tile<W>(a, t, lane, misc);
             __syncwarp();
-            if (lane == 0 && use_single && misc->total == 1 && !(a.dbg & 32)) f_issue_single<W>(a, misc, stage_u32, mbar);
+            if (lane == 0 && use_single && misc->total == 1) f_issue_single<W>(a, misc, stage_u32, mbar);
         }
     } else if (tid == 0) {
         if (t < a.n_tiles) f_issue_tma<W>(a, t, stage_u32, mbar);
@@ -210,6 +239,7 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
     __syncthreads();
 
     unsigned anybits = 0, parity = 0;
+    PT_DECL
     const int f5 = lane & (W - 1), q5 = L::kQPerWarp * warp + lane / W;      // P5/P6 role of this thread
     for (; t < a.n_tiles; t += gridDim.x) {
         const long long f0 = t * W;                        // first frame of the tile, relative to frame_lo
@@ -228,12 +258,32 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
             rem = rem64 > L::kOwn ? L::kOwn : (rem64 < 0 ? 0 : (int)rem64);
             dst = a.vec + (s0 - a.place.lo);
             if (single) {                                        // the span was assembled by bulk copies (f_issue_single)
-                if (!(a.dbg & 32)) { mbar_wait(mbar, parity); parity ^= 1; }
+                mbar_wait(mbar, parity);
+                parity ^= 1;
+            } else if (ztma && !live) {
+                // Empty span: vector samples and PSD columns are zeros.  One thread streams them out of
+                // the zeroed block with bulk stores — no registers, no store instructions, no waiting.
+                if (tid == 0) {
+                    const unsigned zsrc = smem_u32(f_smem + L::kOffZero);
+                    const unsigned bytes = (unsigned)(rem & ~1) * 8u;
+                    for (unsigned off = 0; off < bytes; off += 8192u) {
+                        const unsigned n = bytes - off < 8192u ? bytes - off : 8192u;
+                        tma_bulk_s2g(reinterpret_cast<char *>(dst) + off, zsrc, n);
+                    }
+                    if (rem & 1) __stcs(dst + rem - 1, make_float2(0.f, 0.f));
+                    if (nfr > 0) {
+#pragma unroll
+                        for (int r = 0; r < 8; ++r)
+                            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                                         ::"l"(&a.tmap_z), "r"((int)f0), "r"(128 * r), "r"(zsrc) : "memory");
+                    }
+                    tma_store_commit();
+                }
             } else {
             float4 acc[L::kVec];
 #pragma unroll
             for (int j = 0; j < L::kVec; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (live && !(a.dbg & 32)) {
+            if (live) {
                 for (int p = 0; p < a.place.np; ++p) {
                     const int cnt = misc->cnt[p];
                     if (cnt <= 0) continue;
@@ -247,7 +297,7 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
 #pragma unroll
                             for (int j = 0; j < L::kVec; ++j) {
                                 if (j == L::kVec - 1 && tid >= (L::kLastLive)) break;
-                                const float4 v = (a.dbg & 8) ? __ldcg(reinterpret_cast<const float4 *>(base + 2 * (tid + L::kThreads * j))) : __ldg(reinterpret_cast<const float4 *>(base + 2 * (tid + L::kThreads * j)));
+                                const float4 v = __ldg(reinterpret_cast<const float4 *>(base + 2 * (tid + L::kThreads * j)));
                                 acc[j].x += v.x; acc[j].y += v.y; acc[j].z += v.z; acc[j].w += v.w;
                             }
                         } else {
@@ -257,7 +307,7 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
                                 const int s = 2 * (tid + L::kThreads * j);
                                 const int n = s + rel;
                                 if (n >= -1 && n < len) {        // the bank's zero pads cover n = -1 and n + 1 = len
-                                    const float4 v = (a.dbg & 8) ? __ldcg(reinterpret_cast<const float4 *>(base + s)) : __ldg(reinterpret_cast<const float4 *>(base + s));
+                                    const float4 v = __ldg(reinterpret_cast<const float4 *>(base + s));
                                     acc[j].x += v.x; acc[j].y += v.y; acc[j].z += v.z; acc[j].w += v.w;
                                 }
                             }
@@ -273,7 +323,7 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
                 v.x *= scl; v.y *= scl; v.z *= scl; v.w *= scl;
                 const int s = 2 * (tid + L::kThreads * j);
                 if (live) st4[tid + L::kThreads * j] = v;
-                if (j < L::kVec - 1 && !(a.dbg & 2)) {             // s < L::kOwn: this tile owns the sample
+                if (j < L::kVec - 1) {             // s < L::kOwn: this tile owns the sample
                     if (s + 1 < rem) __stcs(reinterpret_cast<float4 *>(dst + s), v);
                     else if (s < rem) __stcs(dst + s, make_float2(v.x, v.y));
                 }
@@ -283,14 +333,17 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
             mbar_wait(mbar, parity);
             parity ^= 1;
         }
+        PT(0)
+        if (TS && tid == 0) tma_store_wait_read();                 // the last PSD tile has left the exchange memory
         __syncthreads();                                          // A: stage full (and last tile's exchange reads done)
-        if (FUSED && single && tid == 0 && rem > 0 && !(a.dbg & 2)) {   // vector store of a bulk-assembled span: smem -> HBM bulk copy
+        PT(1)
+        if (FUSED && single && tid == 0 && rem > 0) {   // vector store of a bulk-assembled span: smem -> HBM bulk copy
             if (rem > 1) tma_bulk_s2g(dst, stage_u32, (unsigned)(rem & ~1) * 8u);
             tma_store_commit();
             if (rem & 1) __stcs(dst + rem - 1, stage[rem - 1]);
         }
         // ------------------------------------------------------------------ P3 + P4
-        if (live && warp < nfr && !(a.dbg & 64)) {
+        if (live && warp < nfr) {
             cf32 v[32];
             const float2 *sp = stage + warp * hop + lane;
 #pragma unroll
@@ -298,7 +351,9 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
                 const float2 x = sp[32 * brev5(i)];
                 v[i].x = x.x; v[i].y = x.y;
             }
-            if (!(a.dbg & 4)) fft32_windowed(v, wreg);
+            const float4 *wl = win4 + lane;
+            fft32_windowed_q(v, [wl](int k) { const float4 t = wl[32 * k]; return f32x4{t.x, t.y, t.z, t.w}; });
+            PT(2)
             float2 *ex = exch + warp * kExPitch + lane;
 #pragma unroll
             for (int q = 0; q < 32; ++q) ex[32 * q] = make_float2(v[q].x, v[q].y);
@@ -307,20 +362,61 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
             if (t + gridDim.x < a.n_tiles) f_setup_tile<W>(a, t + gridDim.x, lane, misc);   // P1 (next tile)
             if (lane == 0 && single) tma_store_wait_read();      // the vector bulk store has finished reading the stage
         }
+        PT(3)
         __syncthreads();                                          // B: exchange full, stage free
+        PT(4)
         if (tid == 0 && t + gridDim.x < a.n_tiles) {
             if (!FUSED) f_issue_tma<W>(a, t + gridDim.x, stage_u32, mbar);
-            else if (use_single && misc->total == 1 && !(a.dbg & 32)) f_issue_single<W>(a, misc, stage_u32, mbar);
+            else if (use_single && misc->total == 1) f_issue_single<W>(a, misc, stage_u32, mbar);
         }
         // ------------------------------------------------------------------ P5 + P6
-        if (f5 < nfr) {
+        if (TS && live) {
+            // The PSD tile [1024 rows][W frames] is staged in the exchange memory (all of it is in
+            // registers after the loads) and leaves by 2-D bulk tensor stores: no store instructions,
+            // no address arithmetic, and the drain overlaps the next tile's placement and transform.
+            const bool act = f5 < nfr;
+            cf32 v[32];
+            if (act) {
+                const float4 *ex4 = reinterpret_cast<const float4 *>(exch + f5 * kExPitch + q5 * 32);
+#pragma unroll
+                for (int l = 0; l < 32; l += 2) {
+                    const float4 x = ex4[l / 2];
+                    v[brev5(l)].x = x.x; v[brev5(l)].y = x.y;
+                    v[brev5(l + 1)].x = x.z; v[brev5(l + 1)].y = x.w;
+                }
+            }
+            __syncthreads();                                      // C: exchange consumed
+            if (act) {
+                const float2 *tq = tw + q5 * kTwPitch;
+                fft32_twiddled(v, [tq](int l) { const float2 w = tq[l]; return cf32{w.x, w.y}; });
+                PT(5)
+                float *pt = reinterpret_cast<float *>(exch) + q5 * W + f5;
+#pragma unroll
+                for (int sp = 0; sp < 32; ++sp) {                 // output row q + 32 sp holds bin q + 32 s, s = (sp + 16) & 31
+                    const int s = (sp + 16) & 31;
+                    const float p = b2_fma(v[s].x, v[s].x, v[s].y * v[s].y);
+                    anybits |= __float_as_uint(p);
+                    pt[32 * W * sp] = p;
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();                                      // D: PSD tile complete
+            if (tid == 0) {
+                const unsigned src = smem_u32(exch);
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+                    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                                 ::"l"(&a.tmap), "r"((int)f0), "r"(256 * r), "r"(src + (unsigned)(256 * r * W * 4)) : "memory");
+                tma_store_commit();
+            }
+        } else if (f5 < nfr) {
             // row q + 32 sp, sp = 8 hi + lo: four 64-bit row-group bases, 32-bit offsets inside a group
             float *o = a.out + (long long)q5 * a.out_ld + (f0 + f5);
             const unsigned step = 32u * (unsigned)a.out_ld;     // host guarantees 7 * 32 * out_ld < 2^32
             float *og[4];
 #pragma unroll
             for (int h = 0; h < 4; ++h) og[h] = o + (long long)h * 256 * a.out_ld;
-            if (live && !(a.dbg & 64)) {
+            if (live) {
                 cf32 v[32];
                 const float4 *ex4 = reinterpret_cast<const float4 *>(exch + f5 * kExPitch + q5 * 32);
 #pragma unroll
@@ -329,21 +425,25 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
                     v[brev5(l)].x = x.x; v[brev5(l)].y = x.y;
                     v[brev5(l + 1)].x = x.z; v[brev5(l + 1)].y = x.w;
                 }
-                const float2 *tq = tw + q5 * 32;
-                if (!(a.dbg & 4)) fft32_twiddled(v, [tq](int l) { const float2 w = tq[l]; return cf32{w.x, w.y}; });
+                const float2 *tq = tw + q5 * kTwPitch;
+                fft32_twiddled(v, [tq](int l) { const float2 w = tq[l]; return cf32{w.x, w.y}; });
+                PT(5)
 #pragma unroll
                 for (int sp = 0; sp < 32; ++sp) {                 // output row q + 32 sp holds bin q + 32 s, s = (sp + 16) & 31
                     const int s = (sp + 16) & 31;
                     const float p = b2_fma(v[s].x, v[s].x, v[s].y * v[s].y);
                     anybits |= __float_as_uint(p);                // p >= 0 or NaN: non-zero bits <=> p != 0
-                    if (!(a.dbg & 1) || p < 0.0f) __stcs(og[sp >> 3] + (unsigned)(sp & 7) * step, p);
+                    __stcs(og[sp >> 3] + (unsigned)(sp & 7) * step, p);
                 }
-            } else {
+            } else if (!ztma) {
 #pragma unroll
                 for (int sp = 0; sp < 32; ++sp) __stcs(og[sp >> 3] + (unsigned)(sp & 7) * step, 0.0f);
             }
         }
+        PT(6)
     }
+    PT_FLUSH
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     if (a.flag && __syncthreads_or(anybits != 0) && tid == 0) atomicOr(a.flag, 1);
 }
 
@@ -356,6 +456,34 @@ inline int fused_w() {
     return kFWarpsDefault;
 }
 
+typedef CUresult (*TensorMapEncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                      const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// 2-D tensor map of the spectrogram slab this launch writes: dim0 = frames (contiguous), dim1 = 1024
+// rows at pitch out_ld; box = w frames x `rows` rows.  Columns past n_frames are clipped by the hardware,
+// so a partial last tile needs no special case.  Returns false when the layout cannot be described
+// (pitch or base not 16-byte aligned) — the caller then uses the direct-store kernel.
+inline bool make_spec_tmap(CUtensorMap *tm, float *out, long long out_ld, long long n_frames, int w, int rows) {
+    static TensorMapEncodeFn enc = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        cudaDriverEntryPointQueryResult qr;
+        void *fn = nullptr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+            qr == cudaDriverEntryPointSuccess)
+            enc = reinterpret_cast<TensorMapEncodeFn>(fn);
+    }
+    if (!enc || n_frames <= 0 || (out_ld & 3) || (reinterpret_cast<uintptr_t>(out) & 15)) return false;
+    cuuint64_t dims[2] = {(cuuint64_t)n_frames, 1024};
+    cuuint64_t strides[1] = {(cuuint64_t)out_ld * 4};
+    cuuint32_t box[2] = {(cuuint32_t)w, (cuuint32_t)rows};
+    cuuint32_t es[2] = {1, 1};
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, out, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <bool FUSED>
 inline int launch_tile1024(b200vec_ctx *ctx, FArgs &a, long long n_frames, long long n_vec, cudaStream_t st) {
     const int w = fused_w();
@@ -366,8 +494,22 @@ inline int launch_tile1024(b200vec_ctx *ctx, FArgs &a, long long n_frames, long 
     if (a.n_tiles == 0) return 0;
     const long long cap = (long long)ctx->sm_count * (16 / w);
     const long long grid = a.n_tiles < cap ? a.n_tiles : cap;
-    if (w == 8) tile1024_kernel<FUSED, 8><<<(unsigned)grid, FL<8>::kThreads, FL<8>::kSmem, st>>>(a);
-    else tile1024_kernel<FUSED, 16><<<(unsigned)grid, FL<16>::kThreads, FL<16>::kSmem, st>>>(a);
+    if (getenv("B200VEC_DEBUG_OCC")) {
+        int occ = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tile1024_kernel<FUSED, 8, false>, FL<8>::kThreads, FL<8>::kSmem);
+        fprintf(stderr, "[b200vec] tile1024<W=8> resident CTAs/SM: %d (smem %zu B)\n", occ, FL<8>::kSmem);
+    }
+    const char *ts_env = getenv("B200VEC_FUSED_TS");     // "1": PSD tiles leave by bulk tensor stores (measured slower: 360 vs 298 us; A/B only)
+    const bool ts = ts_env && ts_env[0] == '1' && make_spec_tmap(&a.tmap, a.out, a.out_ld, n_frames, w, 256);
+    const char *z_env = getenv("B200VEC_FUSED_ZTMA");    // "1": empty tiles by bulk stores from a zeroed smem block (measured 283 vs 274 us; A/B only)
+    a.ztma = FUSED && w == 16 && z_env && z_env[0] == '1' && make_spec_tmap(&a.tmap_z, a.out, a.out_ld, n_frames, w, 128);
+    if (w == 8) {
+        if (ts) tile1024_kernel<FUSED, 8, true><<<(unsigned)grid, FL<8>::kThreads, FL<8>::kSmem, st>>>(a);
+        else tile1024_kernel<FUSED, 8, false><<<(unsigned)grid, FL<8>::kThreads, FL<8>::kSmem, st>>>(a);
+    } else {
+        if (ts) tile1024_kernel<FUSED, 16, true><<<(unsigned)grid, FL<16>::kThreads, FL<16>::kSmem, st>>>(a);
+        else tile1024_kernel<FUSED, 16, false><<<(unsigned)grid, FL<16>::kThreads, FL<16>::kSmem, st>>>(a);
+    }
     B2_CUDA(cudaGetLastError());
     return 0;
 }
@@ -386,11 +528,20 @@ inline int launch_tile1024_plain(b200vec_ctx *ctx, const S1Args &s, cudaStream_t
     return launch_tile1024<false>(ctx, a, s.n_frames, 0, st);
 }
 
+template <bool FUSED, int W, bool TS>
+inline cudaError_t fused1024_attr() {
+    // Without the carve-out hint the driver sizes shared memory for ONE resident CTA, and the two
+    // 256-thread CTAs per SM of the W = 8 layout silently run one after the other.
+    cudaError_t e = cudaFuncSetAttribute(tile1024_kernel<FUSED, W, TS>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                         (int)cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(tile1024_kernel<FUSED, W, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<W>::kSmem);
+}
 inline int fused1024_setup() {
-    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<true, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<16>::kSmem));
-    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<false, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<16>::kSmem));
-    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<8>::kSmem));
-    B2_CUDA(cudaFuncSetAttribute(tile1024_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<8>::kSmem));
+    B2_CUDA((fused1024_attr<true, 16, true>()));  B2_CUDA((fused1024_attr<true, 16, false>()));
+    B2_CUDA((fused1024_attr<false, 16, true>())); B2_CUDA((fused1024_attr<false, 16, false>()));
+    B2_CUDA((fused1024_attr<true, 8, true>()));   B2_CUDA((fused1024_attr<true, 8, false>()));
+    B2_CUDA((fused1024_attr<false, 8, true>()));  B2_CUDA((fused1024_attr<false, 8, false>()));
     return 0;
 }
 

@@ -86,16 +86,6 @@ __device__ __forceinline__ void p_issue_span(const FArgs &a, const PMisc *m, boo
     if (hi < span) tma_bulk_g2s_chunked(stage_u32 + (unsigned)hi * 8u, reinterpret_cast<const char *>(a.zeros), (unsigned)(span - hi) * 8u, mbar);
 }
 
-#ifdef B2_PIPE_TIMING
-__device__ long long g_pipe_prof[160][16][8];
-#define PT_DECL long long pt_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}; long long pt_last = clock64();
-#define PT(k) { const long long pt_now = clock64(); pt_acc[k] += pt_now - pt_last; pt_last = pt_now; }
-#define PT_FLUSH if (lane == 0) { for (int k = 0; k < 8; ++k) g_pipe_prof[blockIdx.x][warp][k] = pt_acc[k]; }
-#else
-#define PT_DECL
-#define PT(k)
-#define PT_FLUSH
-#endif
 
 template <bool FUSED>
 __global__ void __launch_bounds__(kPThreads, 1)
