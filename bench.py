@@ -152,7 +152,7 @@ def run_ours(args):
     n_own = plan.hi - plan.lo
     n_frames = plan.frame_hi - plan.frame_lo
     vec = torch.empty(n_own, dtype=torch.complex64, device=eng.device)
-    spec = eng.alloc_spectrogram(1024, n_frames)
+    spec = eng.alloc_spectrogram(1024, n_frames, frame_major=not args.rows)   # [1024, frames] view of [frames, 1024] memory
     descs, nd = eng.make_descs(rows)
     max_ranges = eng.max_ranges(rows, total, world, rank)      # this rank's share of one common period + head/tail
     from vector_b200._lib import BUILD_MAXONLY, BUILD_SCALE
@@ -206,16 +206,17 @@ def run_ours(args):
     # ---- e2e through the host-buffer API: H2D packets, D2H vector + spectrogram, every step
     pinned_pk = [(torch.from_numpy(np.ascontiguousarray(y)).pin_memory(), pre) for y, pre in packets]
     out_vec = torch.empty(n_own, dtype=torch.complex64).pin_memory()
-    out_spec = torch.empty(spec.shape, dtype=torch.float32).pin_memory()
+    spec_mem = spec.t() if spec.stride(0) == 1 else spec               # the contiguous side of the buffer
+    out_spec = torch.empty(spec_mem.shape, dtype=torch.float32).pin_memory()
 
     def e2e_step():
         pk = [(t.numpy(), pre) for t, pre in pinned_pk]
         generate.prepare_bank(eng, cfgs, pk, FS)                          # H2D of every packet + shift
         v, s, _ = vdist.build_stft_slab(eng, rows, plan, True, reduce_max, fs=FS, out_vec=vec, out_spec=spec)
         out_vec.copy_(v, non_blocking=True)
-        out_spec.copy_(s, non_blocking=True)
+        out_spec.copy_(s.t() if s.stride(0) == 1 else s, non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        return float(out_spec[512, 0]) + float(out_vec[0].real)          # read the result on the host
+        return float(out_spec.flatten()[512]) + float(out_vec[0].real)   # read the result on the host
 
     e2e_steps = max(2, min(args.steps, 5))
     e2e_step()
@@ -300,6 +301,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--rows", action="store_true",
+                    help="A/B: C-order [1024, frames] spectrogram memory (16-frame tile kernel) instead of "
+                         "frame-major memory (warp-per-frame kernel)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

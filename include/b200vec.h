@@ -126,6 +126,19 @@ int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
                            int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
                            int *nonzero_flag_dev, void *stream);
 
+/* Same step, spectrogram stored FRAME-MAJOR: spec_out_dev[(f-frame_lo)*out_ld + row], out_ld >= 1024
+ * and a multiple of 4, base 16-byte aligned.  The [1024, frames] array the reference hands to its
+ * callers (vector_analyzer/spectrogram_analysis.py:49-53: Sxx after fftshift) is then the transpose
+ * VIEW of this buffer — same shape, dtype and values, Fortran-ordered — and one frame's bins are
+ * 4 KB of contiguous memory, which lets every warp transform and store its own frames with no
+ * block-level synchronisation (wf1024.cuh).  Work items are handed out through a counter owned by
+ * the context: do not run two of these calls concurrently on one context. */
+int b200vec_build_stft1024_fm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                              int64_t slab_lo, int64_t slab_hi, void *vec_out_dev, int mode,
+                              double *maxsq_dev, const float *window_dev, float scale,
+                              int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                              int *nonzero_flag_dev, void *stream);
+
 /* ---- dB map and order statistics (normalize_spectrogram, utils.py:356-404) -----------
  * db      : out[i] = 10*log10(|s[i]| + floor)                      (utils.py:363-368)
  * select  : exact order statistics of a float32 array: ranks[] are 0-based positions in the

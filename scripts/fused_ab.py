@@ -15,9 +15,11 @@ rows = generate.placement_rows(cfgs, info, N, FS)
 plan = vdist.plan_slab(N, 1, 0, 1024, 512, 1, align=512)
 nf = plan.frame_hi - plan.frame_lo
 vec = torch.empty(N, dtype=torch.complex64, device=eng.device)
-spec = eng.alloc_spectrogram(1024, nf)
+spec_rows = eng.alloc_spectrogram(1024, nf)
+spec_fm = eng.alloc_spectrogram(1024, nf, frame_major=True)
+spec = spec_rows
 descs, nd = eng.make_descs(rows)
-KEYS = ("B200VEC_FUSED_W", "B200VEC_FUSED_V", "B200VEC_PIPE", "B200VEC_FUSED_TS", "B200VEC_FUSED_ZTMA")
+KEYS = ("LAYOUT", "B200VEC_WF_V", "B200VEC_FUSED_W", "B200VEC_FUSED_V", "B200VEC_PIPE", "B200VEC_FUSED_TS", "B200VEC_FUSED_ZTMA")
 
 
 def run():
@@ -29,6 +31,8 @@ def timeit(label, env):
     for k in KEYS:
         os.environ.pop(k, None)
     os.environ.update(env)
+    global spec
+    spec = spec_fm if env.get("LAYOUT") == "fm" else spec_rows
     eng._maxsq.zero_()
     eng.build_pass(descs, nd, plan.lo, plan.hi, None, BUILD_MAXONLY)
     for _ in range(3):
@@ -45,7 +49,7 @@ def timeit(label, env):
     return vec.clone(), spec.clone()
 
 
-variants = [dict(kv.split("=") for kv in a.split(",") if kv) for a in sys.argv[1:]] or [{}, {"B200VEC_FUSED_W": "8"}]
+variants = [dict(kv.split("=") for kv in a.split(",") if kv) for a in sys.argv[1:]] or [{}, {"LAYOUT": "fm"}]
 ref = None
 for env in variants:
     out = timeit(str(env), env)

@@ -287,23 +287,29 @@ def test_full_rate_stft_cfg1(eng):
 
 
 # ------------------------------------------------------------------------------ fused build + STFT
-def _fused(eng, cfgs, pk, n, normalize, world=1, rank=0):
+def _fused(eng, cfgs, pk, n, normalize, world=1, rank=0, frame_major=True):
+    """frame_major=True: warp-per-frame kernel (spectrogram memory [frames, 1024], handed out as its
+    transpose view); False: the 16-frame tile kernel writing C-order [1024, frames]."""
     from vector_b200 import dist as vdist, generate
     info = generate.prepare_bank(eng, cfgs, pk, 56e6)
     rows = generate.placement_rows(cfgs, info, n, 56e6)
     plan = vdist.plan_slab(n, world, rank, 1024, 512, 1, align=512)
-    vec, spec, _ = vdist.build_stft_slab(eng, rows, plan, normalize, None, fs=56e6)
+    out_spec = eng.alloc_spectrogram(1024, plan.frame_hi - plan.frame_lo, frame_major=frame_major)
+    vec, spec, _ = vdist.build_stft_slab(eng, rows, plan, normalize, None, fs=56e6, out_spec=out_spec)
+    assert spec.shape == (1024, plan.frame_hi - plan.frame_lo)
     return plan, rows, vec, spec
 
 
+@pytest.mark.parametrize("frame_major", [True, False])
 @pytest.mark.parametrize("name", ["wf_2p5ms_shift_norm", "overlap_5ms", "empty_0p5ms", "cfg1_100ms"])
-def test_fused_build_stft_matches_oracle(eng, name):
+def test_fused_build_stft_matches_oracle(eng, name, frame_major):
     """One kernel for placement + scale + STFT: the vector is bit-identical to the two-pass build,
     the spectrogram meets the oracle bar and is bit-identical to the stand-alone STFT kernel."""
     import vector_b200 as vb
     r = _build(name, eng)
     case = r["case"]
-    plan, rows, vec, spec = _fused(eng, case["configs"], r["packets"], r["n"], case["normalize"])
+    plan, rows, vec, spec = _fused(eng, case["configs"], r["packets"], r["n"], case["normalize"],
+                                   frame_major=frame_major)
     assert torch.equal(vec, r["dev"])
     if r["n"] < 1024:
         assert spec.shape[1] == 0
@@ -319,8 +325,10 @@ def test_fused_build_stft_matches_oracle(eng, name):
     assert torch.equal(spec, S2)
 
 
-@pytest.mark.parametrize("n", [1023, 1024, 1025, 8192, 8193, 8704, 8705, 16 * 512 * 3 + 511, 300_001])
-def test_fused_ragged_lengths(eng, n):
+@pytest.mark.parametrize("frame_major", [True, False])
+@pytest.mark.parametrize("n", [1, 511, 512, 513, 1023, 1024, 1025, 4096, 4607, 4608, 4609, 8192, 8193, 8704, 8705,
+                               16 * 512 * 3 + 511, 300_001])
+def test_fused_ragged_lengths(eng, n, frame_major):
     """Tile edges: vectors shorter than a frame, exactly one tile, odd tails, partial last tiles."""
     import vector_b200 as vb
     from vector_b200 import generate
@@ -329,7 +337,7 @@ def test_fused_ragged_lengths(eng, n):
         c["period"] = max(c["period"], 1e-5)
     pk = [(y[:700], pre) for y, pre in O.packets_for(cfgs)]          # short packets so that they fit
     want = O.build_vector(pk, cfgs, n, True)[0]
-    plan, rows, vec, spec = _fused(eng, cfgs, pk, n, True)
+    plan, rows, vec, spec = _fused(eng, cfgs, pk, n, True, frame_major=frame_major)
     ref, _, _, _ = generate.build_vector_device(cfgs, n, True, packets=pk, engine=eng)
     assert vec.numel() == n and torch.equal(vec, ref)
     assert P.rel_l2(vec.cpu().numpy(), want) <= 3e-7
@@ -342,8 +350,9 @@ def test_fused_ragged_lengths(eng, n):
         assert P.spec_db_error(spec.cpu().numpy(), Sr) <= P.SPEC_DB
 
 
+@pytest.mark.parametrize("frame_major", [True, False])
 @pytest.mark.parametrize("world", [2, 3, 8])
-def test_fused_slabs_concatenate(eng, world):
+def test_fused_slabs_concatenate(eng, world, frame_major):
     """Time-slab sharding of the fused step, ranks emulated one after another on one GPU: slabs and
     spectrogram columns concatenate to the single-GPU result bit for bit."""
     from vector_b200 import dist as vdist, generate
@@ -363,7 +372,7 @@ def test_fused_slabs_concatenate(eng, world):
     vecs, specs = [], []
     for pl in plans:
         v = torch.empty(pl.hi - pl.lo, dtype=torch.complex64, device=eng.device)
-        sp = eng.alloc_spectrogram(1024, pl.frame_hi - pl.frame_lo)
+        sp = eng.alloc_spectrogram(1024, pl.frame_hi - pl.frame_lo, frame_major=frame_major)
         eng.build_stft1024(descs, nd, pl.lo, pl.hi, v, BUILD_SCALE, pl.frame_lo, pl.frame_hi - pl.frame_lo, sp,
                            fs=56e6, maxsq=maxsq)
         vecs.append(v); specs.append(sp)
@@ -380,6 +389,9 @@ def test_fused_full_size(eng):
     pk = O.packets_for(cfgs)
     n = 56_000_000
     plan, rows, vec, spec = _fused(eng, cfgs, pk, n, True)
+    _, _, vec_t, spec_t = _fused(eng, cfgs, pk, n, True, frame_major=False)
+    assert torch.equal(vec, vec_t) and torch.equal(spec, spec_t)       # warp-per-frame == tile kernel
+    del vec_t, spec_t
     ref, _, counts, _ = generate.build_vector_device(cfgs, n, True, packets=pk, engine=eng)
     assert counts == [10, 20, 49, 97, 192, 475]
     assert torch.equal(vec, ref)

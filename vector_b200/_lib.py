@@ -46,6 +46,9 @@ _SIGNATURES = {
     "b200vec_build_stft1024": (C.c_int, [C.c_void_p, C.POINTER(PktDesc), C.c_int, C.c_int64, C.c_int64,
                                          C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_float,
                                          C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "b200vec_build_stft1024_fm": (C.c_int, [C.c_void_p, C.POINTER(PktDesc), C.c_int, C.c_int64, C.c_int64,
+                                            C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_float,
+                                            C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "b200vec_db": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]),
     "b200vec_select_count": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int,
                                        C.POINTER(C.c_int64), C.c_void_p]),

@@ -7,6 +7,7 @@
 #include "stft1024.cuh"
 #include "fused1024.cuh"
 #include "pipe1024.cuh"
+#include "wf1024.cuh"
 #include "select.cuh"
 
 namespace b200vec {
@@ -95,7 +96,7 @@ int b200vec_create(int device, b200vec_ctx **out) {
                                  B200VEC_MAX_RANKS * kBins3 * 4));
     B2_CUDA(cudaFuncSetAttribute(stft_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  200 * 1024));
-    if (stft1024_setup() || fused1024_setup() || pipe1024_setup()) { delete ctx; return 1; }
+    if (stft1024_setup() || fused1024_setup() || pipe1024_setup() || wf1024_setup()) { delete ctx; return 1; }
     *out = ctx;
     return 0;
 }
@@ -112,6 +113,7 @@ int b200vec_destroy(b200vec_ctx *ctx) {
     for (auto &s : ctx->fft64) if (s.ptr) cudaFree(s.ptr);
     if (ctx->hist) cudaFree(ctx->hist);
     if (ctx->zeros) cudaFree(ctx->zeros);
+    if (ctx->wf_ctr) cudaFree(ctx->wf_ctr);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     delete ctx;
     return 0;
@@ -349,6 +351,38 @@ int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
     if (get_tw1024(ctx, &a.tw)) return 1;
     if (pipe1024_enabled()) return launch_pipe1024<true>(ctx, a, n_frames, slab_hi - slab_lo, (cudaStream_t)stream);
     return launch_tile1024<true>(ctx, a, n_frames, slab_hi - slab_lo, (cudaStream_t)stream);
+}
+
+int b200vec_build_stft1024_fm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                              int64_t slab_lo, int64_t slab_hi, void *vec_out_dev, int mode,
+                              double *maxsq_dev, const float *window_dev, float scale,
+                              int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                              int *nonzero_flag_dev, void *stream) {
+    B2_REQUIRE(ctx, "ctx is NULL");
+    B2_REQUIRE(n_pkts >= 0 && n_pkts <= B200VEC_MAX_PACKETS, "too many packets");
+    B2_REQUIRE(n_pkts == 0 || descs, "descs is NULL");
+    B2_REQUIRE(slab_lo >= 0 && slab_hi >= slab_lo, "bad slab");
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || mode == B200VEC_BUILD_SCALE, "mode must be STORE or SCALE");
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || maxsq_dev, "maxsq_dev is NULL");
+    B2_REQUIRE(vec_out_dev || slab_hi == slab_lo, "vec_out_dev is NULL");
+    B2_REQUIRE(((uintptr_t)vec_out_dev & 15) == 0, "vec_out_dev must be 16-byte aligned");
+    B2_REQUIRE(window_dev && (spec_out_dev || n_frames == 0), "NULL argument");
+    B2_REQUIRE(frame_lo >= 0 && n_frames >= 0, "bad geometry");
+    B2_REQUIRE(out_ld >= 1024 && (out_ld & 3) == 0 && ((uintptr_t)spec_out_dev & 15) == 0,
+               "frame-major spectrogram: out_ld >= 1024, a multiple of 4, 16-byte aligned base");
+    B2_REQUIRE(slab_lo == frame_lo * 512, "slab_lo must equal frame_lo * 512 (slabs are cut on hop boundaries)");
+    B2_REQUIRE(n_frames * 512 <= slab_hi - slab_lo + 511, "frames must start inside the slab");
+    WfArgs a;
+    if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place)) return 1;
+    DeviceGuard g(ctx->device);
+    a.vec = (float2 *)vec_out_dev;
+    a.maxsq = reinterpret_cast<const unsigned long long *>(maxsq_dev);
+    a.mode = mode;
+    a.window = window_dev; a.scale = scale;
+    a.n_frames = n_frames; a.out = spec_out_dev; a.out_ld = out_ld;
+    a.flag = nonzero_flag_dev;
+    if (get_tw1024(ctx, &a.tw)) return 1;
+    return launch_wf1024(ctx, a, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------

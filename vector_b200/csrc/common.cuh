@@ -67,5 +67,6 @@ struct b200vec_ctx {
     unsigned int *hist = nullptr;         // select scratch (see select.cuh)
     void *pinned = nullptr;               // small pinned staging block
     float2 *zeros = nullptr;              // one span of zero samples (bulk-copy source, fused1024.cuh)
+    unsigned int *wf_ctr = nullptr;       // work-item counter of the warp-per-frame kernel (wf1024.cuh)
     int sm_count = b200vec::kSmCount;
 };

@@ -1,0 +1,278 @@
+// wf1024.cuh — the BASELINE step (placement + scale + store + nfft = 1024 spectrogram) with every
+// WARP working on its own frames and the spectrogram stored FRAME-MAJOR.
+//
+// Replaces, for the full-rate analysis shape (hann 1024 / hop 512 / nfft 1024, two-sided,
+// vector_analyzer/spectrogram_analysis.py:35-49):
+//   unified_gui.py:1712,1757-1769,1781 (np.zeros, `+=` loop, divide by max)
+//   scipy.signal.spectrogram + fftshift(axes=0)
+//
+// Why a second fused kernel.  The tile kernel (fused1024.cuh) writes the reference's C-order
+// [1024, frames] array directly; 64-byte row runs force 16 frames per tile, a 131 KB exchange
+// buffer, one CTA per SM and two block barriers per tile, so its shared-memory phases, its FP
+// phases and its store phases run one after the other (measured: 163 us skeleton + 74 us FFT
+// + 60 us stores = the 297 us total, profiles/README.md).  Here the spectrogram buffer is
+// [frames, 1024] (the array handed to Python is its transpose VIEW: same shape, dtype and values as
+// the reference's, Fortran-ordered).  One frame's 1024 bins are then 4 KB of contiguous memory, a
+// whole 1024-point transform fits inside ONE warp, and nothing is shared between warps:
+//   * no block barrier in the main loop (two __syncwarp per frame), no TMA, no mbarrier;
+//   * 16 independent warps per SM drift out of phase, so one warp's L2 gather, another's
+//     shared-memory exchange, another's FMAs and another's stores overlap;
+//   * every spectrogram store instruction writes one full 128-byte line at an immediate offset.
+//
+// Work item = kWfChunk consecutive frames, handed out by a global atomic counter (dynamic: live
+// and empty stretches of the vector cost very different amounts).  Per item a warp
+//   S   finds, per packet (lane p), the instance range overlapping the item's span
+//       (two 64-bit floor divisions), once;
+//   B   builds the next 512 samples: lane l owns x[l + 32 j]; for every overlapping
+//       (packet, instance) in the reference's order it adds the packet samples (8-byte loads,
+//       256 B per warp instruction, from the L2-resident bank), scales, and streams them to the
+//       vector (each sample is stored by exactly one item);
+//   T1  first 32-point transform over j with the window folded in (fft32.cuh) on
+//       [previous 512 | new 512], results to the warp's private exchange block [l][q] (pitch 33);
+//   T2  lane q reads B_l[q] for all l, second transform with the W1024 twiddles folded in,
+//       |X|^2 -> out[f][ (k + 512) mod 1024 ], k = q + 32 s.
+// HBM traffic: 8 B/sample vector store + 8 B/sample spectrogram store, nothing read.
+#pragma once
+#include "common.cuh"
+#include "place.cuh"
+#include "fft32.cuh"
+#include "stft1024.cuh"      // get_tw1024
+
+namespace b200vec {
+
+constexpr int kWfWarps = 16;
+constexpr int kWfThreads = 32 * kWfWarps;
+constexpr int kWfChunk = 8;                                       // frames per work item
+constexpr int kWfExPitch = 33;                                    // float2 per l-row of a warp's exchange block
+constexpr size_t kWfOffExch = 0;
+constexpr size_t kWfOffTw = kWfOffExch + (size_t)kWfWarps * 32 * kWfExPitch * sizeof(float2);
+constexpr size_t kWfOffWin = kWfOffTw + 32 * 32 * sizeof(float2);
+constexpr size_t kWfSmem = kWfOffWin + 1024 * sizeof(float);
+
+struct WfArgs {
+    PlaceArgs place;             // descriptors + the vector slab [lo, hi) this launch stores; lo = frame_lo * 512
+    float2 *vec;                 // vec[0] = sample place.lo
+    const unsigned long long *maxsq;
+    int mode;                    // B200VEC_BUILD_STORE or B200VEC_BUILD_SCALE
+    const float *window;         // 1024 taps
+    const float2 *tw;            // [l][q] = exp(-2*pi*i*l*q/1024)  (symmetric)
+    float scale;
+    long long n_frames;          // frames [frame_lo, frame_lo + n_frames)
+    float *out;                  // out[(f - frame_lo) * out_ld + row]
+    long long out_ld;            // >= 1024, multiple of 4
+    int *flag;
+    long long n_chunks;
+    unsigned int *ctr;           // [0] next work item, [1] finished CTAs (both zero between launches)
+};
+
+// B: the 512 samples starting `off` samples into the item's span.  Returns false when no packet
+// instance overlaps them (x is then exactly zero).
+__device__ __forceinline__ bool wf_build_half(const WfArgs &a, unsigned active, int cnt_l, int rel0_l, int off,
+                                              int lane, float2 (&x)[16]) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] = make_float2(0.f, 0.f);
+    bool live = false;
+    for (unsigned m = active; m; m &= m - 1) {
+        const int p = __ffs(m) - 1;
+        const int cnt = __shfl_sync(0xffffffffu, cnt_l, p);
+        const int rel0 = __shfl_sync(0xffffffffu, rel0_l, p);
+        const PlaceDesc &d = a.place.d[p];
+        const int len = d.len;
+        const long long period = d.period;
+        long long r64 = (long long)rel0 + off;               // packet index of x's sample 0 for instance klo + i
+        for (int i = 0; i < cnt; ++i, r64 -= period) {
+            if (r64 + 512 <= 0) break;                       // this and every later instance start after the half
+            if (r64 >= len) continue;                        // instance ended before the half
+            const int r = (int)r64;
+            live = true;
+            const float2 *base = d.a + r + lane;
+            if (r >= 0 && r + 512 <= len) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float2 v = __ldg(base + 32 * j);
+                    x[j].x += v.x; x[j].y += v.y;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const int n = r + lane + 32 * j;
+                    if (n >= 0 && n < len) {
+                        const float2 v = __ldg(base + 32 * j);
+                        x[j].x += v.x; x[j].y += v.y;
+                    }
+                }
+            }
+        }
+    }
+    return live;
+}
+
+// scale + store half h (slab-relative samples [s, s + 512)); n_vec = samples this launch stores
+__device__ __forceinline__ void wf_store_half(float2 *vec, long long s, long long n_vec, bool live, float scl,
+                                              int lane, float2 (&x)[16]) {
+    if (live) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { x[j].x *= scl; x[j].y *= scl; }
+    }
+    if (s >= n_vec) return;
+    float2 *dst = vec + s;
+    if (s + 512 <= n_vec) {
+        if (live) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) __stcs(dst + lane + 32 * j, x[j]);
+        } else {                                             // zeros: 16-byte stores, 512 B per warp instruction
+            float4 *d4 = reinterpret_cast<float4 *>(dst) + lane;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) __stcs(d4 + 32 * k, make_float4(0.f, 0.f, 0.f, 0.f));
+        }
+    } else {
+        const int rem = (int)(n_vec - s);
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+            if (lane + 32 * j < rem) __stcs(dst + lane + 32 * j, x[j]);
+    }
+}
+
+__global__ void __launch_bounds__(kWfThreads, 1)
+wf1024_kernel(const __grid_constant__ WfArgs a) {
+    extern __shared__ __align__(16) unsigned char w_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float2 *exch = reinterpret_cast<float2 *>(w_smem + kWfOffExch) + warp * (32 * kWfExPitch);
+    float2 *tw = reinterpret_cast<float2 *>(w_smem + kWfOffTw);
+    float4 *win4 = reinterpret_cast<float4 *>(w_smem + kWfOffWin);
+
+    for (int i = tid; i < 1024; i += kWfThreads) tw[i] = __ldg(a.tw + i);
+    {
+        const float rs = sqrtf(a.scale);                    // |X|^2 * scale = |FFT(x * w * sqrt(scale))|^2
+        float *wf = reinterpret_cast<float *>(win4);
+        for (int i = tid; i < 1024; i += kWfThreads) {      // i = (k * 32 + lane) * 4 + c  ->  tap j = brev5(4 k + c) of lane
+            const int c = i & 3, ln = (i >> 2) & 31, k = i >> 7;
+            wf[i] = __ldg(a.window + ln + 32 * brev5(4 * k + c)) * rs;
+        }
+    }
+    float scl = 1.0f;
+    if (a.mode == B200VEC_BUILD_SCALE) {
+        const double m2 = __longlong_as_double((long long)*a.maxsq);
+        if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);        // numpy's complex64 / float32: multiply by the fp32 reciprocal
+    }
+    __syncthreads();
+
+    const long long n_vec = a.place.hi - a.place.lo;
+    const float4 *wl = win4 + lane;
+    const float2 *tq = tw + lane;
+    float2 *ex_w = exch + lane * kWfExPitch;                 // T1 writes row l = lane
+    const float2 *ex_r = exch + lane;                        // T2 reads column q = lane
+    unsigned anybits = 0;
+
+    unsigned next = 0;
+    if (lane == 0) next = atomicAdd(a.ctr, 1u);
+    for (;;) {
+        const long long c = __shfl_sync(0xffffffffu, next, 0);
+        if (c >= a.n_chunks) break;
+        if (lane == 0) next = atomicAdd(a.ctr, 1u);         // the next item's index arrives while this one is processed
+        const long long h0 = c * kWfChunk;                   // first half-frame / frame of the item (slab-relative)
+        // ---------------------------------------------------------------- S
+        int cnt_l = 0, rel0_l = 0;
+        if (lane < a.place.np) {
+            const PlaceDesc &d = a.place.d[lane];
+            const long long s0 = a.place.lo + h0 * 512;
+            long long klo = floor_div(s0 - d.len - d.start, d.period) + 1;
+            long long khi = floor_div(s0 + (kWfChunk + 1) * 512 - 1 - d.start, d.period);
+            if (klo < 0) klo = 0;
+            if (khi > d.count - 1) khi = d.count - 1;
+            const long long cn = khi - klo + 1;
+            cnt_l = cn > 0 ? (int)(cn < 0x00ffffff ? cn : 0x00ffffff) : 0;
+            rel0_l = cnt_l ? (int)(s0 - (d.start + klo * d.period)) : 0;
+        }
+        const unsigned active = __ballot_sync(0xffffffffu, cnt_l > 0);
+
+        float2 xo[16], xn[16];
+        bool live_o = wf_build_half(a, active, cnt_l, rel0_l, 0, lane, xo);
+        wf_store_half(a.vec, h0 * 512, n_vec, live_o, scl, lane, xo);
+#pragma unroll 1
+        for (int i = 0; i < kWfChunk; ++i) {
+            const long long h = h0 + i;
+            const bool fv = h < a.n_frames;                                   // frame h exists
+            const bool sv = (i + 1 < kWfChunk) && (h + 1) * 512 < n_vec;      // this item stores half h + 1
+            if (!fv && !sv) break;
+            const bool live_n = wf_build_half(a, active, cnt_l, rel0_l, (i + 1) * 512, lane, xn);
+            wf_store_half(a.vec, sv ? (h + 1) * 512 : n_vec, n_vec, live_n, scl, lane, xn);
+            if (fv) {
+                float *of = a.out + h * a.out_ld;
+                if (live_o || live_n) {
+                    // ------------------------------------------------------ T1
+                    cf32 v[32];
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) {           // v[k] = x[brev5(k)]
+                        const int j = brev5(k);
+                        const float2 s = j < 16 ? xo[j] : xn[j - 16];
+                        v[k].x = s.x; v[k].y = s.y;
+                    }
+                    fft32_windowed_q(v, [wl](int k) { const float4 t = wl[32 * k]; return f32x4{t.x, t.y, t.z, t.w}; });
+#pragma unroll
+                    for (int q = 0; q < 32; ++q) ex_w[q] = make_float2(v[q].x, v[q].y);
+                    __syncwarp();
+                    // ------------------------------------------------------ T2
+#pragma unroll
+                    for (int l = 0; l < 32; ++l) {           // v[brev5(l)] = B_l[q]
+                        const float2 s = ex_r[l * kWfExPitch];
+                        v[brev5(l)].x = s.x; v[brev5(l)].y = s.y;
+                    }
+                    __syncwarp();                            // the block may be overwritten by the next frame
+                    fft32_twiddled(v, [tq](int l) { const float2 w = tq[32 * l]; return cf32{w.x, w.y}; });
+                    float *o = of + lane;
+#pragma unroll
+                    for (int sp = 0; sp < 32; ++sp) {        // row q + 32 sp holds bin q + 32 s, s = (sp + 16) & 31
+                        const int s = (sp + 16) & 31;
+                        const float p = b2_fma(v[s].x, v[s].x, v[s].y * v[s].y);
+                        anybits |= __float_as_uint(p);       // p >= 0 or NaN: non-zero bits <=> p != 0
+                        __stcs(o + 32 * sp, p);
+                    }
+                } else {
+                    float4 *o4 = reinterpret_cast<float4 *>(of) + lane;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) __stcs(o4 + 32 * k, make_float4(0.f, 0.f, 0.f, 0.f));
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) xo[j] = xn[j];
+            live_o = live_n;
+        }
+    }
+    if (a.flag && __any_sync(0xffffffffu, anybits != 0) && lane == 0) atomicOr(a.flag, 1);
+    __syncthreads();
+    if (tid == 0) {                                          // the last CTA out re-arms the counters for the next launch
+        __threadfence();
+        const unsigned done = atomicAdd(a.ctr + 1, 1u);
+        if (done == gridDim.x - 1) { a.ctr[0] = 0; a.ctr[1] = 0; __threadfence(); }
+    }
+}
+
+inline int wf1024_setup() {
+    B2_CUDA(cudaFuncSetAttribute(wf1024_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 (int)cudaSharedmemCarveoutMaxShared));
+    B2_CUDA(cudaFuncSetAttribute(wf1024_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWfSmem));
+    return 0;
+}
+
+inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
+    const long long n_vec = a.place.hi - a.place.lo;
+    const long long halves = (n_vec + 511) / 512;
+    const long long units = a.n_frames > halves ? a.n_frames : halves;
+    a.n_chunks = (units + kWfChunk - 1) / kWfChunk;
+    if (a.n_chunks == 0) return 0;
+    B2_REQUIRE(a.n_chunks < 0x7fffffffLL, "slab too long for one launch (split it)");
+    if (!ctx->wf_ctr) {
+        B2_CUDA(cudaMalloc(&ctx->wf_ctr, 2 * sizeof(unsigned int)));
+        B2_CUDA(cudaMemsetAsync(ctx->wf_ctr, 0, 2 * sizeof(unsigned int), st));
+    }
+    a.ctr = ctx->wf_ctr;
+    const long long cap = ctx->sm_count;
+    const long long need = (a.n_chunks + kWfWarps - 1) / kWfWarps;
+    const unsigned grid = (unsigned)(need < cap ? need : cap);
+    wf1024_kernel<<<grid, kWfThreads, kWfSmem, st>>>(a);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace b200vec

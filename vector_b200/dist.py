@@ -96,7 +96,7 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
     if out_vec is None:
         out_vec = torch.empty(max(n, 0), dtype=torch.complex64, device=engine.device)
     if out_spec is None:
-        out_spec = engine.alloc_spectrogram(1024, nf)
+        out_spec = engine.alloc_spectrogram(1024, nf, frame_major=True)
     descs, nd = engine.make_descs(rows)
     mode = BUILD_STORE
     if normalize:

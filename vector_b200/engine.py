@@ -144,13 +144,18 @@ class Engine:
                        window="hann", fs=H.TARGET_SAMPLE_RATE, scaling="density", maxsq=None, flag=None):
         """Fused pass B + full-rate STFT (nperseg = nfft = 1024, hop 512): samples [lo, hi) of the
         vector into vec_out, frames [frame_lo, frame_lo+n_frames) into spec_out, one kernel, the
-        vector never re-read.  lo must equal frame_lo*512."""
+        vector never re-read.  lo must equal frame_lo*512.  spec_out is a float32 [1024, n_frames]
+        tensor; its strides pick the kernel: frame-major memory (stride(0) == 1, what
+        alloc_spectrogram(..., frame_major=True) returns) runs the warp-per-frame kernel
+        (b200vec_build_stft1024_fm), row-major memory the 16-frame tile kernel."""
         maxsq = self._maxsq if maxsq is None else maxsq
         taps, scale = self.window(window, 1024, fs, scaling)
-        check(self.lib.b200vec_build_stft1024(
-            self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), mode, self._ptr(maxsq),
-            self._ptr(taps), scale, int(frame_lo), int(n_frames), self._ptr(spec_out),
-            spec_out.stride(0), self._ptr(flag) if flag is not None else None, self._stream()))
+        frame_major = spec_out.dim() == 2 and spec_out.stride(0) == 1 and spec_out.stride(1) >= 1024
+        fn = self.lib.b200vec_build_stft1024_fm if frame_major else self.lib.b200vec_build_stft1024
+        check(fn(self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), mode, self._ptr(maxsq),
+                 self._ptr(taps), scale, int(frame_lo), int(n_frames), self._ptr(spec_out),
+                 spec_out.stride(1) if frame_major else spec_out.stride(0),
+                 self._ptr(flag) if flag is not None else None, self._stream()))
         self.launches += 1
 
     # ------------------------------------------------------------------ spectrogram
@@ -161,9 +166,14 @@ class Engine:
             self._windows[key] = (torch.from_numpy(taps.astype(np.float32)).to(self.device), float(scale))
         return self._windows[key]
 
-    def alloc_spectrogram(self, nfft, n_frames):
-        """float32 [nfft, n_frames] view whose rows start on 128-byte boundaries (row pitch
-        rounded up to 32 floats), so the kernels' per-row runs never straddle sectors."""
+    def alloc_spectrogram(self, nfft, n_frames, frame_major=False):
+        """float32 [nfft, n_frames] tensor for a spectrogram.
+        frame_major=False: C-order rows whose starts sit on 128-byte boundaries (row pitch rounded
+        up to 32 floats), so the kernels' per-row runs never straddle sectors.
+        frame_major=True: the transpose view of a contiguous [n_frames, nfft] buffer — same shape,
+        dtype and values for every consumer, one frame's bins contiguous in memory."""
+        if frame_major:
+            return torch.empty((max(n_frames, 0), nfft), dtype=torch.float32, device=self.device).t()
         pitch = (n_frames + 31) // 32 * 32
         return torch.empty((nfft, max(pitch, 32)), dtype=torch.float32, device=self.device)[:, :n_frames]
 
