@@ -37,17 +37,22 @@
 #include "place.cuh"
 #include "fft32.cuh"
 #include "stft1024.cuh"      // get_tw1024
+#include "fused1024.cuh"     // tma_bulk_s2g, tma_store_commit
 
 namespace b200vec {
 
 constexpr int kWfWarps = 16;
 constexpr int kWfThreads = 32 * kWfWarps;
-constexpr int kWfChunk = 8;                                       // frames per work item
+constexpr int kWfChunk = 4;                                       // frames per work item (default; B200VEC_WF_CHUNK=4|8 for A/B: 190 vs 203 us)
 constexpr int kWfExPitch = 33;                                    // float2 per l-row of a warp's exchange block
 constexpr size_t kWfOffExch = 0;
 constexpr size_t kWfOffTw = kWfOffExch + (size_t)kWfWarps * 32 * kWfExPitch * sizeof(float2);
 constexpr size_t kWfOffWin = kWfOffTw + 32 * 32 * sizeof(float2);
-constexpr size_t kWfSmem = kWfOffWin + 1024 * sizeof(float);
+constexpr size_t kWfSmemDirect = kWfOffWin + 1024 * sizeof(float);
+// bulk-store variant: one 4 KB staging block per warp for the vector half + one shared block of zeros
+constexpr size_t kWfOffVst = kWfSmemDirect;
+constexpr size_t kWfOffZero = kWfOffVst + (size_t)kWfWarps * 4096;
+constexpr size_t kWfSmemBulk = kWfOffZero + 4096;
 
 struct WfArgs {
     PlaceArgs place;             // descriptors + the vector slab [lo, hi) this launch stores; lo = frame_lo * 512
@@ -61,6 +66,7 @@ struct WfArgs {
     float *out;                  // out[(f - frame_lo) * out_ld + row]
     long long out_ld;            // >= 1024, multiple of 4
     int *flag;
+    long long n_big;             // work items [0, n_big) are CHUNK frames long, the rest one frame
     long long n_chunks;
     unsigned int *ctr;           // [0] next work item, [1] finished CTAs (both zero between launches)
 };
@@ -107,17 +113,39 @@ __device__ __forceinline__ bool wf_build_half(const WfArgs &a, unsigned active, 
     return live;
 }
 
-// scale + store half h (slab-relative samples [s, s + 512)); n_vec = samples this launch stores
+__device__ __forceinline__ void wf_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void wf_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// scale + store half h (slab-relative samples [s, s + 512)); n_vec = samples this launch stores.
+// BULK: whole halves leave through the warp's 4 KB staging block as ONE bulk copy (cp.async.bulk
+// shared -> global) issued by lane 0 — the store then occupies neither registers nor the LSU queue
+// that the shared-memory exchange of the other warps needs; zero halves are copied from the block
+// of zeros.  Before a staging block is rewritten lane 0 waits until its bulk copies have finished
+// READING shared memory (wait_group.read 0): the copy issued last is at least one L2 gather or one
+// 32-point transform old by then, so the wait is normally free.
+template <bool STORE, bool BULK>
 __device__ __forceinline__ void wf_store_half(float2 *vec, long long s, long long n_vec, bool live, float scl,
-                                              int lane, float2 (&x)[16]) {
+                                              int lane, float2 (&x)[16], float2 *vst, unsigned zero_u32) {
     if (live) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) { x[j].x *= scl; x[j].y *= scl; }
     }
-    if (s >= n_vec) return;
+    if (!STORE || s >= n_vec) return;
     float2 *dst = vec + s;
     if (s + 512 <= n_vec) {
-        if (live) {
+        if (BULK) {
+            if (live) {
+                if (lane == 0) wf_wait_read();
+                __syncwarp();
+#pragma unroll
+                for (int j = 0; j < 16; ++j) vst[lane + 32 * j] = x[j];
+                wf_fence_async();
+                __syncwarp();
+                if (lane == 0) { tma_bulk_s2g(dst, smem_u32(vst), 4096u); tma_store_commit(); }
+            } else if (lane == 0) {
+                tma_bulk_s2g(dst, zero_u32, 4096u); tma_store_commit();
+            }
+        } else if (live) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) __stcs(dst + lane + 32 * j, x[j]);
         } else {                                             // zeros: 16-byte stores, 512 B per warp instruction
@@ -133,6 +161,9 @@ __device__ __forceinline__ void wf_store_half(float2 *vec, long long s, long lon
     }
 }
 
+// CHUNK = frames per work item.  DBG (timing experiments only, results are wrong when non-zero):
+// bit 0 drops the spectrogram stores, bit 1 the vector stores, bit 2 both transforms.
+template <int CHUNK, int DBG, bool BULK>
 __global__ void __launch_bounds__(kWfThreads, 1)
 wf1024_kernel(const __grid_constant__ WfArgs a) {
     extern __shared__ __align__(16) unsigned char w_smem[];
@@ -140,6 +171,13 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
     float2 *exch = reinterpret_cast<float2 *>(w_smem + kWfOffExch) + warp * (32 * kWfExPitch);
     float2 *tw = reinterpret_cast<float2 *>(w_smem + kWfOffTw);
     float4 *win4 = reinterpret_cast<float4 *>(w_smem + kWfOffWin);
+    float2 *vst = reinterpret_cast<float2 *>(w_smem + kWfOffVst) + warp * 512;      // BULK only
+    const unsigned zero_u32 = smem_u32(w_smem + kWfOffZero);                        // BULK only
+    if (BULK) {
+        for (int i = tid; i < 256; i += kWfThreads)
+            reinterpret_cast<float4 *>(w_smem + kWfOffZero)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        wf_fence_async();
+    }
 
     for (int i = tid; i < 1024; i += kWfThreads) tw[i] = __ldg(a.tw + i);
     {
@@ -170,14 +208,16 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         const long long c = __shfl_sync(0xffffffffu, next, 0);
         if (c >= a.n_chunks) break;
         if (lane == 0) next = atomicAdd(a.ctr, 1u);         // the next item's index arrives while this one is processed
-        const long long h0 = c * kWfChunk;                   // first half-frame / frame of the item (slab-relative)
+        const bool big = c < a.n_big;
+        const int cn = big ? CHUNK : 1;                      // frames in this item
+        const long long h0 = big ? c * CHUNK : a.n_big * CHUNK + (c - a.n_big);   // its first half-frame / frame (slab-relative)
         // ---------------------------------------------------------------- S
         int cnt_l = 0, rel0_l = 0;
         if (lane < a.place.np) {
             const PlaceDesc &d = a.place.d[lane];
             const long long s0 = a.place.lo + h0 * 512;
             long long klo = floor_div(s0 - d.len - d.start, d.period) + 1;
-            long long khi = floor_div(s0 + (kWfChunk + 1) * 512 - 1 - d.start, d.period);
+            long long khi = floor_div(s0 + (cn + 1) * 512 - 1 - d.start, d.period);
             if (klo < 0) klo = 0;
             if (khi > d.count - 1) khi = d.count - 1;
             const long long cn = khi - klo + 1;
@@ -188,15 +228,15 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
 
         float2 xo[16], xn[16];
         bool live_o = wf_build_half(a, active, cnt_l, rel0_l, 0, lane, xo);
-        wf_store_half(a.vec, h0 * 512, n_vec, live_o, scl, lane, xo);
+        wf_store_half<!(DBG & 2), BULK>(a.vec, h0 * 512, n_vec, live_o, scl, lane, xo, vst, zero_u32);
 #pragma unroll 1
-        for (int i = 0; i < kWfChunk; ++i) {
+        for (int i = 0; i < cn; ++i) {
             const long long h = h0 + i;
             const bool fv = h < a.n_frames;                                   // frame h exists
-            const bool sv = (i + 1 < kWfChunk) && (h + 1) * 512 < n_vec;      // this item stores half h + 1
+            const bool sv = (i + 1 < cn) && (h + 1) * 512 < n_vec;      // this item stores half h + 1
             if (!fv && !sv) break;
             const bool live_n = wf_build_half(a, active, cnt_l, rel0_l, (i + 1) * 512, lane, xn);
-            wf_store_half(a.vec, sv ? (h + 1) * 512 : n_vec, n_vec, live_n, scl, lane, xn);
+            wf_store_half<!(DBG & 2), BULK>(a.vec, sv ? (h + 1) * 512 : n_vec, n_vec, live_n, scl, lane, xn, vst, zero_u32);
             if (fv) {
                 float *of = a.out + h * a.out_ld;
                 if (live_o || live_n) {
@@ -208,7 +248,11 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                         const float2 s = j < 16 ? xo[j] : xn[j - 16];
                         v[k].x = s.x; v[k].y = s.y;
                     }
-                    fft32_windowed_q(v, [wl](int k) { const float4 t = wl[32 * k]; return f32x4{t.x, t.y, t.z, t.w}; });
+                    if (!(DBG & 4)) fft32_windowed_q(v, [wl](int k) { const float4 t = wl[32 * k]; return f32x4{t.x, t.y, t.z, t.w}; });
+                    if (BULK) {                              // the last PSD frame has left the exchange block
+                        if (lane == 0) wf_wait_read();
+                        __syncwarp();
+                    }
 #pragma unroll
                     for (int q = 0; q < 32; ++q) ex_w[q] = make_float2(v[q].x, v[q].y);
                     __syncwarp();
@@ -219,19 +263,28 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                         v[brev5(l)].x = s.x; v[brev5(l)].y = s.y;
                     }
                     __syncwarp();                            // the block may be overwritten by the next frame
-                    fft32_twiddled(v, [tq](int l) { const float2 w = tq[32 * l]; return cf32{w.x, w.y}; });
-                    float *o = of + lane;
+                    if (!(DBG & 4)) fft32_twiddled(v, [tq](int l) { const float2 w = tq[32 * l]; return cf32{w.x, w.y}; });
+                    // BULK: the frame's 4 KB are staged in the (now free) exchange block and leave as one bulk copy
+                    float *o = BULK ? reinterpret_cast<float *>(exch) + lane : of + lane;
 #pragma unroll
                     for (int sp = 0; sp < 32; ++sp) {        // row q + 32 sp holds bin q + 32 s, s = (sp + 16) & 31
                         const int s = (sp + 16) & 31;
                         const float p = b2_fma(v[s].x, v[s].x, v[s].y * v[s].y);
                         anybits |= __float_as_uint(p);       // p >= 0 or NaN: non-zero bits <=> p != 0
-                        __stcs(o + 32 * sp, p);
+                        if (BULK) o[32 * sp] = p;
+                        else if (!(DBG & 1)) __stcs(o + 32 * sp, p);
                     }
+                    if (BULK) {
+                        wf_fence_async();
+                        __syncwarp();
+                        if (lane == 0 && !(DBG & 1)) { tma_bulk_s2g(of, smem_u32(exch), 4096u); tma_store_commit(); }
+                    }
+                } else if (BULK) {
+                    if (lane == 0 && !(DBG & 1)) { tma_bulk_s2g(of, zero_u32, 4096u); tma_store_commit(); }
                 } else {
                     float4 *o4 = reinterpret_cast<float4 *>(of) + lane;
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) __stcs(o4 + 32 * k, make_float4(0.f, 0.f, 0.f, 0.f));
+                    for (int k = 0; k < 8; ++k) if (!(DBG & 1)) __stcs(o4 + 32 * k, make_float4(0.f, 0.f, 0.f, 0.f));
                 }
             }
 #pragma unroll
@@ -239,6 +292,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
             live_o = live_n;
         }
     }
+    if (BULK && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     if (a.flag && __any_sync(0xffffffffu, anybits != 0) && lane == 0) atomicOr(a.flag, 1);
     __syncthreads();
     if (tid == 0) {                                          // the last CTA out re-arms the counters for the next launch
@@ -248,18 +302,43 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
     }
 }
 
+template <int CHUNK, int DBG, bool BULK>
+inline cudaError_t wf1024_attr() {
+    cudaError_t e = cudaFuncSetAttribute(wf1024_kernel<CHUNK, DBG, BULK>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                         (int)cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(wf1024_kernel<CHUNK, DBG, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(BULK ? kWfSmemBulk : kWfSmemDirect));
+}
 inline int wf1024_setup() {
-    B2_CUDA(cudaFuncSetAttribute(wf1024_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                 (int)cudaSharedmemCarveoutMaxShared));
-    B2_CUDA(cudaFuncSetAttribute(wf1024_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWfSmem));
+    B2_CUDA((wf1024_attr<4, 0, true>())); B2_CUDA((wf1024_attr<8, 0, true>())); B2_CUDA((wf1024_attr<2, 0, true>()));
+    B2_CUDA((wf1024_attr<4, 0, false>())); B2_CUDA((wf1024_attr<8, 0, false>())); B2_CUDA((wf1024_attr<2, 0, false>()));
+#ifdef B2_WF_ABLATION
+    B2_CUDA((wf1024_attr<4, 1, false>())); B2_CUDA((wf1024_attr<4, 2, false>())); B2_CUDA((wf1024_attr<4, 3, false>()));
+    B2_CUDA((wf1024_attr<4, 4, false>())); B2_CUDA((wf1024_attr<4, 7, false>()));
+#endif
     return 0;
 }
 
 inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
+    int chunk = kWfChunk, dbg = 0;
+    bool bulk = true;
+    if (const char *e = getenv("B200VEC_WF_CHUNK")) chunk = atoi(e);
+    if (const char *e = getenv("B200VEC_WF_V")) dbg = atoi(e);
+    if (const char *e = getenv("B200VEC_WF_BULK")) bulk = e[0] != '0';      // "0": direct STG stores (A/B)
+    bool tail = true;
+    if (const char *e = getenv("B200VEC_WF_TAIL")) tail = e[0] != '0';      // "0": no single-frame items at the end (A/B)
+    B2_REQUIRE(chunk == 2 || chunk == 4 || chunk == 8, "B200VEC_WF_CHUNK must be 2, 4 or 8");
     const long long n_vec = a.place.hi - a.place.lo;
     const long long halves = (n_vec + 511) / 512;
     const long long units = a.n_frames > halves ? a.n_frames : halves;
-    a.n_chunks = (units + kWfChunk - 1) / kWfChunk;
+    // Guided tail: the last ~2 items' worth of frames per warp are handed out one frame at a time, so
+    // the warps run dry within one frame time of each other instead of one item time.
+    const long long n_warps = (long long)ctx->sm_count * kWfWarps;
+    long long singles = tail ? 2 * n_warps : 0;
+    if (singles > units) singles = units;
+    a.n_big = (units - singles) / chunk;
+    a.n_chunks = a.n_big + (units - a.n_big * chunk);
     if (a.n_chunks == 0) return 0;
     B2_REQUIRE(a.n_chunks < 0x7fffffffLL, "slab too long for one launch (split it)");
     if (!ctx->wf_ctr) {
@@ -270,7 +349,31 @@ inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
     const long long cap = ctx->sm_count;
     const long long need = (a.n_chunks + kWfWarps - 1) / kWfWarps;
     const unsigned grid = (unsigned)(need < cap ? need : cap);
-    wf1024_kernel<<<grid, kWfThreads, kWfSmem, st>>>(a);
+#define B2_WF_LAUNCH(C, D, B) wf1024_kernel<C, D, B><<<grid, kWfThreads, (B) ? kWfSmemBulk : kWfSmemDirect, st>>>(a)
+    if (dbg == 0) {
+        const int sel = (chunk == 8 ? 4 : chunk == 2 ? 2 : 0) | (bulk ? 1 : 0);
+        switch (sel) {
+            case 0: B2_WF_LAUNCH(4, 0, false); break;
+            case 1: B2_WF_LAUNCH(4, 0, true); break;
+            case 2: B2_WF_LAUNCH(2, 0, false); break;
+            case 3: B2_WF_LAUNCH(2, 0, true); break;
+            case 4: B2_WF_LAUNCH(8, 0, false); break;
+            default: B2_WF_LAUNCH(8, 0, true); break;
+        }
+    } else {
+#ifdef B2_WF_ABLATION
+        switch (dbg) {
+            case 1: B2_WF_LAUNCH(4, 1, false); break;
+            case 2: B2_WF_LAUNCH(4, 2, false); break;
+            case 3: B2_WF_LAUNCH(4, 3, false); break;
+            case 4: B2_WF_LAUNCH(4, 4, false); break;
+            default: B2_WF_LAUNCH(4, 7, false); break;
+        }
+#else
+        return fail("launch_wf1024", "B200VEC_WF_V needs a -DB2_WF_ABLATION build");
+#endif
+    }
+#undef B2_WF_LAUNCH
     B2_CUDA(cudaGetLastError());
     return 0;
 }
