@@ -6,7 +6,8 @@ One step = one pass of the hot path over one batch of synthetic input:
     pass A (max |v|^2 over one common period of the packet trains + head/tail, no stores)
     -> [all-reduce MAX of one double when N > 1] ->
     ONE fused kernel: recompute, scale, store complex64 AND the full-rate STFT (hann 1024/512,
-    nfft 1024, 'density', fftshifted float32 [1024, frames]) out of shared memory
+    nfft 1024, 'density', fftshifted float32 [1024, frames] handed out as the transpose view of
+    frame-major memory) — every warp builds, transforms and stores its own frames
 on SURVEY.md §8d cfg2 (6 packets, periods 100/50/20/10/5/2 ms, shifts +2/-3/+1/-8/+6/-12 MHz,
 normalisation on).  At N GPUs the vector is N x 1000 ms long and time-sharded, 56 M samples
 (+ halo) per GPU: per-GPU work is fixed -> "scaling": "weak".  value = all samples / max-over-
@@ -246,6 +247,7 @@ def run_ours(args):
         for k in kernels.values():
             k["GBps"] = k["alg_bytes"] / (k["ms"] * 1e-3) / 1e9 if k["ms"] > 0 else None
         dom = "build_stft1024(fused passB+STFT)"
+        kname = "tile1024_kernel<1,16,0> (C-order rows)" if args.rows else "wf1024_kernel (warp per frame, frame-major memory)"
         ach = kernels[dom]["GBps"]
         line = {
             "metric": METRIC, "value": total / (ms_step * 1e-3) / 1e9, "unit": "GSa/s", "n_gpus": world,
@@ -255,7 +257,7 @@ def run_ours(args):
             "config": {"workload": WORKLOAD, "samples_per_gpu": N_PER_GPU, "total_samples": total,
                        "parallelism": f"time-slab x{world}, 1 scalar all-reduce(MAX)" if world > 1 else "single GPU",
                        "l2": "no flush: each step writes 896 MB per GPU (vector + spectrogram), far above the 126 MB L2"},
-            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": dom, "cuda_kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_nominal_8000": ach / 8000.0, "traffic": None,
                          "peak_source": peak_src,
                          "step_frac": fused_bytes / (ms_step * 1e-3) / 1e9 / peak},
