@@ -139,6 +139,20 @@ int b200vec_build_stft1024_fm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, i
                               int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
                               int *nonzero_flag_dev, void *stream);
 
+/* The whole normalised step in ONE launch (single-GPU builds; unified_gui.py:1778-1782 folded in):
+ * the kernel first reduces max |v|^2 over the sample ranges norm_ranges[2r] .. norm_ranges[2r+1]
+ * (host array of n_ranges <= 4 [lo, hi) pairs, vector-absolute; the caller passes ranges whose max
+ * is the max of the whole vector — the entire vector, or one common period of the packet trains
+ * plus head and tail), meets at a grid barrier (cooperative launch) and then runs the SCALE pass of
+ * b200vec_build_stft1024_fm with that max.  *maxsq_dev (optional) receives max |v|^2.  A multi-GPU
+ * build keeps the two-launch form: b200vec_build(MAXONLY), all-reduce MAX, ..._fm(SCALE). */
+int b200vec_build_stft1024_fm_norm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                                   int64_t slab_lo, int64_t slab_hi, void *vec_out_dev,
+                                   const int64_t *norm_ranges, int n_ranges, double *maxsq_dev,
+                                   const float *window_dev, float scale,
+                                   int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                                   int *nonzero_flag_dev, void *stream);
+
 /* ---- dB map and order statistics (normalize_spectrogram, utils.py:356-404) -----------
  * db      : out[i] = 10*log10(|s[i]| + floor)                      (utils.py:363-368)
  * select  : exact order statistics of a float32 array: ranks[] are 0-based positions in the

@@ -1,5 +1,11 @@
 #!/bin/bash
 mkdir -p gpurun_out
-python scripts/fused_ab.py LAYOUT=fm LAYOUT=fm,B200VEC_WF_TAIL=0 LAYOUT=fm,B200VEC_WF_CHUNK=8 LAYOUT=fm,B200VEC_WF_CHUNK=2 LAYOUT=fm,B200VEC_WF_CHUNK=2,B200VEC_WF_TAIL=0 LAYOUT=fm,B200VEC_WF_BULK=0 LAYOUT=fm,B200VEC_WF_BULK=0,B200VEC_WF_CHUNK=2 > gpurun_out/wf_ab.txt 2>&1
-timeout 600 python -m pytest tests -m gpu -q -x -k "fused" 2>&1 | tail -3
-cat gpurun_out/wf_ab.txt
+timeout 900 python -m pytest tests -m gpu -q -x 2>&1 | tail -4
+python bench.py --steps 20 --warmup 3 --no-cpu > gpurun_out/bench_one.json 2> gpurun_out/bench_one.err; tail -2 gpurun_out/bench_one.err
+python bench.py --steps 20 --warmup 3 --no-cpu --two-launch > gpurun_out/bench_two.json 2>&1
+python - <<'PY'
+import json
+for f in ("bench_one","bench_two"):
+    d=json.load(open(f"gpurun_out/{f}.json"))
+    print(f, d["value"], d["ms_per_step"], {k:v["ms"] for k,v in d["kernels"].items()}, d["roofline"]["frac"], d["e2e"]["value"], d["gpu_launches"])
+PY

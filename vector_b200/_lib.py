@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libb200vec.so")
+LIB_PATH = os.environ.get("B200VEC_LIB") or os.path.join(_HERE, "csrc", "libb200vec.so")   # B200VEC_LIB: A/B builds
 
 MAX_PACKETS = 32
 MAX_SLOTS = 64
@@ -49,6 +49,10 @@ _SIGNATURES = {
     "b200vec_build_stft1024_fm": (C.c_int, [C.c_void_p, C.POINTER(PktDesc), C.c_int, C.c_int64, C.c_int64,
                                             C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_float,
                                             C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "b200vec_build_stft1024_fm_norm": (C.c_int, [C.c_void_p, C.POINTER(PktDesc), C.c_int, C.c_int64, C.c_int64,
+                                                 C.c_void_p, C.POINTER(C.c_int64), C.c_int, C.c_void_p,
+                                                 C.c_void_p, C.c_float, C.c_int64, C.c_int64, C.c_void_p,
+                                                 C.c_int64, C.c_void_p, C.c_void_p]),
     "b200vec_db": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]),
     "b200vec_select_count": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int,
                                        C.POINTER(C.c_int64), C.c_void_p]),

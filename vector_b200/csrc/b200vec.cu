@@ -353,17 +353,18 @@ int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
     return launch_tile1024<true>(ctx, a, n_frames, slab_hi - slab_lo, (cudaStream_t)stream);
 }
 
-int b200vec_build_stft1024_fm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
-                              int64_t slab_lo, int64_t slab_hi, void *vec_out_dev, int mode,
-                              double *maxsq_dev, const float *window_dev, float scale,
-                              int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
-                              int *nonzero_flag_dev, void *stream) {
+static int build_stft1024_fm_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                                  int64_t slab_lo, int64_t slab_hi, void *vec_out_dev, int mode,
+                                  const int64_t *norm_ranges, int n_ranges,
+                                  double *maxsq_dev, const float *window_dev, float scale,
+                                  int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                                  int *nonzero_flag_dev, void *stream) {
     B2_REQUIRE(ctx, "ctx is NULL");
     B2_REQUIRE(n_pkts >= 0 && n_pkts <= B200VEC_MAX_PACKETS, "too many packets");
     B2_REQUIRE(n_pkts == 0 || descs, "descs is NULL");
     B2_REQUIRE(slab_lo >= 0 && slab_hi >= slab_lo, "bad slab");
-    B2_REQUIRE(mode == B200VEC_BUILD_STORE || mode == B200VEC_BUILD_SCALE, "mode must be STORE or SCALE");
-    B2_REQUIRE(mode == B200VEC_BUILD_STORE || maxsq_dev, "maxsq_dev is NULL");
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || mode == B200VEC_BUILD_SCALE || mode == kWfAutoNorm, "bad mode");
+    B2_REQUIRE(mode != B200VEC_BUILD_SCALE || maxsq_dev, "maxsq_dev is NULL");
     B2_REQUIRE(vec_out_dev || slab_hi == slab_lo, "vec_out_dev is NULL");
     B2_REQUIRE(((uintptr_t)vec_out_dev & 15) == 0, "vec_out_dev must be 16-byte aligned");
     B2_REQUIRE(window_dev && (spec_out_dev || n_frames == 0), "NULL argument");
@@ -374,6 +375,18 @@ int b200vec_build_stft1024_fm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, i
     B2_REQUIRE(n_frames * 512 <= slab_hi - slab_lo + 511, "frames must start inside the slab");
     WfArgs a;
     if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place)) return 1;
+    a.n_norm = 0; a.norm_units = 0; a.maxsq_out = nullptr;
+    if (mode == kWfAutoNorm) {
+        B2_REQUIRE(n_ranges >= 0 && n_ranges <= kWfMaxNormRanges && (n_ranges == 0 || norm_ranges), "bad norm ranges");
+        for (int r = 0; r < n_ranges; ++r) {
+            const int64_t lo = norm_ranges[2 * r], hi = norm_ranges[2 * r + 1];
+            B2_REQUIRE(lo >= 0 && hi >= lo, "bad norm range");
+            if (hi == lo) continue;
+            a.norm_lo[a.n_norm] = lo; a.norm_hi[a.n_norm] = hi; ++a.n_norm;
+            a.norm_units += (hi - lo + 1023) / 1024;
+        }
+        a.maxsq_out = maxsq_dev;
+    }
     DeviceGuard g(ctx->device);
     a.vec = (float2 *)vec_out_dev;
     a.maxsq = reinterpret_cast<const unsigned long long *>(maxsq_dev);
@@ -383,6 +396,27 @@ int b200vec_build_stft1024_fm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, i
     a.flag = nonzero_flag_dev;
     if (get_tw1024(ctx, &a.tw)) return 1;
     return launch_wf1024(ctx, a, (cudaStream_t)stream);
+}
+
+int b200vec_build_stft1024_fm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                              int64_t slab_lo, int64_t slab_hi, void *vec_out_dev, int mode,
+                              double *maxsq_dev, const float *window_dev, float scale,
+                              int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                              int *nonzero_flag_dev, void *stream) {
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || mode == B200VEC_BUILD_SCALE, "mode must be STORE or SCALE");
+    return build_stft1024_fm_impl(ctx, descs, n_pkts, slab_lo, slab_hi, vec_out_dev, mode, nullptr, 0, maxsq_dev,
+                                  window_dev, scale, frame_lo, n_frames, spec_out_dev, out_ld, nonzero_flag_dev, stream);
+}
+
+int b200vec_build_stft1024_fm_norm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                                   int64_t slab_lo, int64_t slab_hi, void *vec_out_dev,
+                                   const int64_t *norm_ranges, int n_ranges, double *maxsq_dev,
+                                   const float *window_dev, float scale,
+                                   int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                                   int *nonzero_flag_dev, void *stream) {
+    return build_stft1024_fm_impl(ctx, descs, n_pkts, slab_lo, slab_hi, vec_out_dev, kWfAutoNorm, norm_ranges, n_ranges,
+                                  maxsq_dev, window_dev, scale, frame_lo, n_frames, spec_out_dev, out_ld,
+                                  nonzero_flag_dev, stream);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -44,6 +44,8 @@ namespace b200vec {
 constexpr int kWfWarps = 16;
 constexpr int kWfThreads = 32 * kWfWarps;
 constexpr int kWfChunk = 4;                                       // frames per work item (default; B200VEC_WF_CHUNK=4|8 for A/B: 190 vs 203 us)
+constexpr int kWfMaxNormRanges = 4;
+constexpr int kWfAutoNorm = 3;                                    // WfArgs::mode: find the max in-kernel, then scale
 constexpr int kWfExPitch = 33;                                    // float2 per l-row of a warp's exchange block
 constexpr size_t kWfOffExch = 0;
 constexpr size_t kWfOffTw = kWfOffExch + (size_t)kWfWarps * 32 * kWfExPitch * sizeof(float2);
@@ -68,7 +70,12 @@ struct WfArgs {
     int *flag;
     long long n_big;             // work items [0, n_big) are CHUNK frames long, the rest one frame
     long long n_chunks;
-    unsigned int *ctr;           // [0] next work item, [1] finished CTAs (both zero between launches)
+    // in-kernel normalisation (mode == kWfAutoNorm): max |v|^2 over these sample ranges first
+    long long norm_lo[kWfMaxNormRanges], norm_hi[kWfMaxNormRanges];
+    long long norm_units;        // 1024-sample units over all ranges (a range's last unit may be partial)
+    int n_norm;
+    double *maxsq_out;           // receives max |v|^2 (may be NULL)
+    unsigned int *ctr;           // [0] next work item, [1] finished CTAs, [2] grid barrier, [4..5] max |v|^2 bits (all zero between launches)
 };
 
 // B: the 512 samples starting `off` samples into the item's span.  Returns false when no packet
@@ -194,6 +201,63 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);        // numpy's complex64 / float32: multiply by the fp32 reciprocal
     }
     __syncthreads();
+    if (a.mode == kWfAutoNorm) {
+        // Pass A inside the kernel (single-GPU builds): every warp evaluates its share of the ranges whose
+        // max is the max of the whole vector (hostmath.max_eval_ranges), the grid meets at a barrier
+        // (cooperative launch: all CTAs are resident), and everybody reads the same exact max.
+        unsigned long long *slot = reinterpret_cast<unsigned long long *>(a.ctr + 4);
+        double tmax = 0.0;                                   // running max of |v|^2 (exact products in fp64)
+        float fthr = 0.0f;                                   // fp32 pre-filter threshold
+        const long long gw = (long long)blockIdx.x * kWfWarps + warp, nw = (long long)gridDim.x * kWfWarps;
+        for (long long u = gw; u < a.norm_units; u += nw) {
+            long long v = u, s0 = 0, s1 = 0;
+            for (int r = 0; r < a.n_norm; ++r) {
+                const long long nu = (a.norm_hi[r] - a.norm_lo[r] + 1023) / 1024;
+                if (v < nu) { s0 = a.norm_lo[r] + v * 1024; s1 = a.norm_hi[r]; break; }
+                v -= nu;
+            }
+            if (s1 > s0 + 1024) s1 = s0 + 1024;
+            int cnt_l = 0, rel0_l = 0;
+            if (lane < a.place.np) {
+                const PlaceDesc &d = a.place.d[lane];
+                long long klo = floor_div(s0 - d.len - d.start, d.period) + 1;
+                long long khi = floor_div(s0 + 1024 - 1 - d.start, d.period);
+                if (klo < 0) klo = 0;
+                if (khi > d.count - 1) khi = d.count - 1;
+                const long long cn = khi - klo + 1;
+                cnt_l = cn > 0 ? (int)(cn < 0x00ffffff ? cn : 0x00ffffff) : 0;
+                rel0_l = cnt_l ? (int)(s0 - (d.start + klo * d.period)) : 0;
+            }
+            const unsigned active = __ballot_sync(0xffffffffu, cnt_l > 0);
+            for (int half = 0; half < 2; ++half) {
+                const int valid = (int)(s1 - s0) - 512 * half;
+                if (valid <= 0) break;
+                float2 x[16];
+                if (!wf_build_half(a, active, cnt_l, rel0_l, 512 * half, lane, x)) continue;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float q = (lane + 32 * j < valid) ? x[j].x * x[j].x + x[j].y * x[j].y : 0.f;
+                    if (q >= fthr) {
+                        const double e = (double)x[j].x * (double)x[j].x + (double)x[j].y * (double)x[j].y;
+                        if (e > tmax) { tmax = e; fthr = q * 0.99999f; }
+                    }
+                }
+            }
+        }
+        tmax = warp_max(tmax);
+        if (lane == 0 && tmax > 0.0) atomicMax(slot, (unsigned long long)__double_as_longlong(tmax));
+        __syncthreads();
+        if (tid == 0) {                                      // grid barrier
+            __threadfence();
+            atomicAdd(a.ctr + 2, 1u);
+            while (*reinterpret_cast<volatile unsigned int *>(a.ctr + 2) < gridDim.x) __nanosleep(40);
+            __threadfence();
+        }
+        __syncthreads();
+        const double m2 = __longlong_as_double((long long)*reinterpret_cast<volatile unsigned long long *>(slot));
+        if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);
+        if (blockIdx.x == 0 && tid == 0 && a.maxsq_out) *a.maxsq_out = m2;
+    }
 
     const long long n_vec = a.place.hi - a.place.lo;
     const float4 *wl = win4 + lane;
@@ -298,7 +362,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
     if (tid == 0) {                                          // the last CTA out re-arms the counters for the next launch
         __threadfence();
         const unsigned done = atomicAdd(a.ctr + 1, 1u);
-        if (done == gridDim.x - 1) { a.ctr[0] = 0; a.ctr[1] = 0; __threadfence(); }
+        if (done == gridDim.x - 1) { a.ctr[0] = 0; a.ctr[1] = 0; a.ctr[2] = 0; a.ctr[4] = 0; a.ctr[5] = 0; __threadfence(); }
     }
 }
 
@@ -342,14 +406,23 @@ inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
     if (a.n_chunks == 0) return 0;
     B2_REQUIRE(a.n_chunks < 0x7fffffffLL, "slab too long for one launch (split it)");
     if (!ctx->wf_ctr) {
-        B2_CUDA(cudaMalloc(&ctx->wf_ctr, 2 * sizeof(unsigned int)));
-        B2_CUDA(cudaMemsetAsync(ctx->wf_ctr, 0, 2 * sizeof(unsigned int), st));
+        B2_CUDA(cudaMalloc(&ctx->wf_ctr, 8 * sizeof(unsigned int)));
+        B2_CUDA(cudaMemsetAsync(ctx->wf_ctr, 0, 8 * sizeof(unsigned int), st));
     }
     a.ctr = ctx->wf_ctr;
     const long long cap = ctx->sm_count;
     const long long need = (a.n_chunks + kWfWarps - 1) / kWfWarps;
     const unsigned grid = (unsigned)(need < cap ? need : cap);
-#define B2_WF_LAUNCH(C, D, B) wf1024_kernel<C, D, B><<<grid, kWfThreads, (B) ? kWfSmemBulk : kWfSmemDirect, st>>>(a)
+    // the in-kernel max needs a grid barrier: cooperative launch (all CTAs resident, or the launch fails)
+    void *kargs[] = {&a};
+#define B2_WF_LAUNCH(C, D, B)                                                                              \
+    do {                                                                                                   \
+        if (a.mode == kWfAutoNorm)                                                                         \
+            B2_CUDA(cudaLaunchCooperativeKernel((const void *)wf1024_kernel<C, D, B>, dim3(grid), dim3(kWfThreads), \
+                                                kargs, (B) ? kWfSmemBulk : kWfSmemDirect, st));            \
+        else                                                                                               \
+            wf1024_kernel<C, D, B><<<grid, kWfThreads, (B) ? kWfSmemBulk : kWfSmemDirect, st>>>(a);        \
+    } while (0)
     if (dbg == 0) {
         const int sel = (chunk == 8 ? 4 : chunk == 2 ? 2 : 0) | (bulk ? 1 : 0);
         switch (sel) {

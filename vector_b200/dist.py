@@ -98,13 +98,19 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
     if out_spec is None:
         out_spec = engine.alloc_spectrogram(1024, nf, frame_major=True)
     descs, nd = engine.make_descs(rows)
-    mode = BUILD_STORE
-    if normalize:
+    mode, norm_ranges = BUILD_STORE, None
+    frame_major = out_spec.dim() == 2 and out_spec.stride(0) == 1 and out_spec.stride(1) >= 1024
+    if normalize and plan.world == 1 and reduce_max is None and frame_major:
+        # single GPU: pass A runs inside the fused kernel (grid barrier), ONE launch for the step
+        norm_ranges = engine.max_ranges(rows, plan.total, 1, 0)
+        if len(norm_ranges) > 4:
+            norm_ranges = [(0, plan.total)]
+    elif normalize:
         engine._maxsq.zero_()
         engine.max_pass(descs, nd, engine.max_ranges(rows, plan.total, plan.world, plan.rank))
         if reduce_max is not None:
             reduce_max(engine._maxsq)
         mode = BUILD_SCALE
     engine.build_stft1024(descs, nd, plan.lo, plan.hi, out_vec, mode, frame_lo, nf, out_spec,
-                          window=window, fs=fs, scaling=scaling)
+                          window=window, fs=fs, scaling=scaling, norm_ranges=norm_ranges)
     return out_vec, out_spec, (engine._maxsq if normalize else None)

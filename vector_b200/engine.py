@@ -141,21 +141,36 @@ class Engine:
         return out, self._maxsq
 
     def build_stft1024(self, descs, n_descs, lo, hi, vec_out, mode, frame_lo, n_frames, spec_out,
-                       window="hann", fs=H.TARGET_SAMPLE_RATE, scaling="density", maxsq=None, flag=None):
+                       window="hann", fs=H.TARGET_SAMPLE_RATE, scaling="density", maxsq=None, flag=None,
+                       norm_ranges=None):
         """Fused pass B + full-rate STFT (nperseg = nfft = 1024, hop 512): samples [lo, hi) of the
         vector into vec_out, frames [frame_lo, frame_lo+n_frames) into spec_out, one kernel, the
         vector never re-read.  lo must equal frame_lo*512.  spec_out is a float32 [1024, n_frames]
         tensor; its strides pick the kernel: frame-major memory (stride(0) == 1, what
         alloc_spectrogram(..., frame_major=True) returns) runs the warp-per-frame kernel
-        (b200vec_build_stft1024_fm), row-major memory the 16-frame tile kernel."""
+        (b200vec_build_stft1024_fm), row-major memory the 16-frame tile kernel.
+        norm_ranges (frame-major only): [(lo, hi), ...] sample ranges whose max |v| is the max of the
+        whole vector (max_ranges()) — the kernel then finds the max itself, scales by it and writes
+        max |v|^2 to maxsq: the whole normalised step in ONE launch (`mode` is ignored)."""
         maxsq = self._maxsq if maxsq is None else maxsq
         taps, scale = self.window(window, 1024, fs, scaling)
         frame_major = spec_out.dim() == 2 and spec_out.stride(0) == 1 and spec_out.stride(1) >= 1024
-        fn = self.lib.b200vec_build_stft1024_fm if frame_major else self.lib.b200vec_build_stft1024
-        check(fn(self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), mode, self._ptr(maxsq),
-                 self._ptr(taps), scale, int(frame_lo), int(n_frames), self._ptr(spec_out),
-                 spec_out.stride(1) if frame_major else spec_out.stride(0),
-                 self._ptr(flag) if flag is not None else None, self._stream()))
+        ld = spec_out.stride(1) if frame_major else spec_out.stride(0)
+        fl = self._ptr(flag) if flag is not None else None
+        if norm_ranges is not None:
+            if not frame_major:
+                raise ValueError("in-kernel normalisation needs frame-major spectrogram memory")
+            flat = [int(v) for r in norm_ranges for v in r]
+            arr = (C.c_int64 * max(len(flat), 1))(*flat)
+            check(self.lib.b200vec_build_stft1024_fm_norm(
+                self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), arr, len(flat) // 2,
+                self._ptr(maxsq), self._ptr(taps), scale, int(frame_lo), int(n_frames), self._ptr(spec_out),
+                ld, fl, self._stream()))
+        else:
+            fn = self.lib.b200vec_build_stft1024_fm if frame_major else self.lib.b200vec_build_stft1024
+            check(fn(self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), mode, self._ptr(maxsq),
+                     self._ptr(taps), scale, int(frame_lo), int(n_frames), self._ptr(spec_out), ld, fl,
+                     self._stream()))
         self.launches += 1
 
     # ------------------------------------------------------------------ spectrogram
