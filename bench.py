@@ -255,6 +255,14 @@ def run_ours(args):
         }
         for k in kernels.values():
             k["GBps"] = k["alg_bytes"] / (k["ms"] * 1e-3) / 1e9 if k["ms"] > 0 else None
+        traffic = None
+        try:                                                   # per-launch DRAM bytes of the dominant kernel, from the committed ncu capture
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+                t = json.load(fh)["wf1024_kernel"]
+            if not args.rows and world == 1:
+                traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
+        except Exception:
+            traffic = None
         dom = "build_stft1024(fused passB+STFT)"
         kname = "tile1024_kernel<1,16,0> (C-order rows)" if args.rows else "wf1024_kernel (warp per frame, frame-major memory)"
         ach = kernels[dom]["GBps"]
@@ -267,7 +275,9 @@ def run_ours(args):
                        "parallelism": f"time-slab x{world}, 1 scalar all-reduce(MAX)" if world > 1 else "single GPU",
                        "l2": "no flush: each step writes 896 MB per GPU (vector + spectrogram), far above the 126 MB L2"},
             "roofline": {"bound": "hbm", "kernel": dom, "cuda_kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "frac_of_nominal_8000": ach / 8000.0, "traffic": None,
+                         "frac": ach / peak, "frac_of_nominal_8000": ach / 8000.0, "traffic": traffic,
+                         "traffic_source": "profiles/ncu_traffic.json (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)" if traffic else None,
+                         "alg_bytes_per_launch": fused_bytes,
                          "peak_source": peak_src,
                          "step_frac": fused_bytes / (ms_step * 1e-3) / 1e9 / peak},
             "kernels": kernels,
