@@ -142,6 +142,7 @@ def run_ours(args):
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # stdout carries exactly one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = get_engine(local)
     cfgs, packets, total = workload(world)
@@ -191,6 +192,32 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
+    # The step is 1 launch at N=1 and memset + 2 launches + 1 all-reduce + 1 launch at N>1: capture it in a
+    # CUDA graph so that the timed loop replays device work back to back (no Python / launch gaps).
+    graph = None
+    launches_per_step = None
+    if not args.no_graph and world == 1:       # N > 1: eager (an NCCL all-reduce inside a captured step hung on this stack)
+        try:
+            l0 = eng.launches
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                step(); step()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            l0 = eng.launches
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                step()
+            launches_per_step = eng.launches - l0
+            g.replay()
+            torch.cuda.synchronize()
+            graph = g
+        except Exception as exc:                                   # capture unsupported: time the eager loop
+            print(f"[bench] CUDA graph capture failed ({type(exc).__name__}: {exc}); eager loop", file=sys.stderr)
+            graph = None
+            torch.cuda.synchronize()
+    barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -200,11 +227,18 @@ def run_ours(args):
     t_start, t_end = ev(), ev()
     t_start.record()
     for _ in range(args.steps):
-        step(marks)
+        if graph is not None:
+            graph.replay()
+        else:
+            step(marks)
     t_end.record()
     barrier()
     ms_total = t_start.elapsed_time(t_end)
-    launches = eng.launches - launches0
+    launches = launches_per_step * args.steps if graph is not None else eng.launches - launches0
+    if graph is not None:                                          # per-kernel split: a few eager steps after the timed region
+        for _ in range(min(args.steps, 10)):
+            step(marks)
+        barrier()
     clocks = sampler.stop() if rank == 0 else None
     ms_t = torch.tensor([ms_total], dtype=torch.float64, device=eng.device)
     if world > 1:
@@ -273,7 +307,8 @@ def run_ours(args):
             "dtype": "complex64/f32 (phase fp64)", "data": "synthetic",
             "config": {"workload": WORKLOAD, "samples_per_gpu": N_PER_GPU, "total_samples": total,
                        "parallelism": f"time-slab x{world}, 1 scalar all-reduce(MAX)" if world > 1 else "single GPU",
-                       "l2": "no flush: each step writes 896 MB per GPU (vector + spectrogram), far above the 126 MB L2"},
+                       "l2": "no flush: each step writes 896 MB per GPU (vector + spectrogram), far above the 126 MB L2",
+                       "timed_loop": "CUDA graph replay of one step, K times" if graph is not None else "eager launches"},
             "roofline": {"bound": "hbm", "kernel": dom, "cuda_kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_nominal_8000": ach / 8000.0, "traffic": traffic,
                          "traffic_source": "profiles/ncu_traffic.json (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)" if traffic else None,
@@ -322,6 +357,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replays")
     ap.add_argument("--two-launch", action="store_true",
                     help="A/B at N=1: pass A as its own launch (the multi-GPU form) instead of inside the fused kernel")
     ap.add_argument("--rows", action="store_true",
