@@ -153,6 +153,14 @@ int b200vec_build_stft1024_fm_norm(b200vec_ctx *ctx, const b200vec_pkt_desc *des
                                    int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
                                    int *nonzero_flag_dev, void *stream);
 
+/* b200vec_stft for the full-rate analysis shape (hann-type window of 1024 taps, nperseg = nfft = 1024,
+ * hop 512, stride 1; vector_analyzer/spectrogram_analysis.py:40-53, mat_analyzer.py:37-45) with the
+ * spectrogram stored FRAME-MAJOR: out_dev[(f-frame_lo)*out_ld + row] (see b200vec_build_stft1024_fm).
+ * in_dev[0] is vector sample in_origin; 16 B per output sample of HBM traffic (8 read + 8 written). */
+int b200vec_stft1024_fm(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_t in_len,
+                        const float *window_dev, float scale, int64_t frame_lo, int64_t n_frames,
+                        float *out_dev, int64_t out_ld, int *nonzero_flag_dev, void *stream);
+
 /* ---- dB map and order statistics (normalize_spectrogram, utils.py:356-404) -----------
  * db      : out[i] = 10*log10(|s[i]| + floor)                      (utils.py:363-368)
  * select  : exact order statistics of a float32 array: ranks[] are 0-based positions in the

@@ -286,6 +286,28 @@ def test_full_rate_stft_cfg1(eng):
     _check_spec(S.cpu().numpy(), Sr, St)
 
 
+@pytest.mark.parametrize("n", [1024, 1535, 1536, 5000, 70_000, 300_001])
+def test_full_rate_stft_frame_major_equals_rows(eng, n):
+    """b200vec_stft1024_fm (warp-per-frame kernel, frame-major memory) == the C-order tile kernel, bit
+    for bit, on noise (no exact zeros), whole-vector and slab-relative calls; the oracle bar holds."""
+    rng = np.random.default_rng(n)
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+    x[n // 3: n // 3 + 2000] = 0                                       # an all-zero stretch: exact-zero frames
+    d = torch.from_numpy(x).to(eng.device)
+    A = eng.stft(d, "hann", 1024, 512, 1024, 56e6)                     # frame-major default
+    B = eng.stft(d, "hann", 1024, 512, 1024, 56e6, frame_major=False)
+    assert A.shape == B.shape == (1024, (n - 1024) // 512 + 1)
+    assert A.stride(0) == 1 and (B.stride(1) == 1 or B.shape[1] == 1)
+    assert torch.equal(A, B)
+    _, _, Sr = O.full_rate_spectrogram(x, 56e6)
+    assert P.spec_db_error(A.cpu().numpy(), Sr) <= P.SPEC_DB
+    if A.shape[1] > 3:                                                 # slab-relative: origin != 0, frame_lo != 0
+        f_lo = 2
+        part = eng.stft(d[f_lo * 512 - 10:], "hann", 1024, 512, 1024, 56e6, in_origin=f_lo * 512 - 10,
+                        frame_lo=f_lo, n_frames=A.shape[1] - f_lo, total_len=n)
+        assert torch.equal(part, A[:, f_lo:])
+
+
 # ------------------------------------------------------------------------------ fused build + STFT
 def _fused(eng, cfgs, pk, n, normalize, world=1, rank=0, frame_major=True):
     """frame_major=True: warp-per-frame kernel (spectrogram memory [frames, 1024], handed out as its

@@ -375,7 +375,7 @@ static int build_stft1024_fm_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *desc
     B2_REQUIRE(n_frames * 512 <= slab_hi - slab_lo + 511, "frames must start inside the slab");
     WfArgs a;
     if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place)) return 1;
-    a.n_norm = 0; a.norm_units = 0; a.maxsq_out = nullptr;
+    a.n_norm = 0; a.norm_units = 0; a.maxsq_out = nullptr; a.plain = 0;
     if (mode == kWfAutoNorm) {
         B2_REQUIRE(n_ranges >= 0 && n_ranges <= kWfMaxNormRanges && (n_ranges == 0 || norm_ranges), "bad norm ranges");
         for (int r = 0; r < n_ranges; ++r) {
@@ -417,6 +417,30 @@ int b200vec_build_stft1024_fm_norm(b200vec_ctx *ctx, const b200vec_pkt_desc *des
     return build_stft1024_fm_impl(ctx, descs, n_pkts, slab_lo, slab_hi, vec_out_dev, kWfAutoNorm, norm_ranges, n_ranges,
                                   maxsq_dev, window_dev, scale, frame_lo, n_frames, spec_out_dev, out_ld,
                                   nonzero_flag_dev, stream);
+}
+
+int b200vec_stft1024_fm(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_t in_len,
+                        const float *window_dev, float scale, int64_t frame_lo, int64_t n_frames,
+                        float *out_dev, int64_t out_ld, int *nonzero_flag_dev, void *stream) {
+    B2_REQUIRE(ctx && in_dev && window_dev && (out_dev || n_frames == 0), "NULL argument");
+    B2_REQUIRE(in_len >= 0 && frame_lo >= 0 && n_frames >= 0, "bad geometry");
+    B2_REQUIRE(out_ld >= 1024 && (out_ld & 3) == 0 && ((uintptr_t)out_dev & 15) == 0,
+               "frame-major spectrogram: out_ld >= 1024, a multiple of 4, 16-byte aligned base");
+    if (n_frames == 0) return 0;
+    const long long first = frame_lo * 512 - in_origin;
+    const long long last = (frame_lo + n_frames - 1) * 512 + 1023 - in_origin;
+    B2_REQUIRE(first >= 0 && last < in_len, "frames read outside the input buffer");
+    WfArgs a;
+    memset(&a, 0, sizeof(a));
+    a.plain = 1;
+    a.vec = const_cast<float2 *>((const float2 *)in_dev) + first;
+    a.mode = B200VEC_BUILD_STORE;
+    a.window = window_dev; a.scale = scale;
+    a.n_frames = n_frames; a.out = out_dev; a.out_ld = out_ld;
+    a.flag = nonzero_flag_dev;
+    DeviceGuard g(ctx->device);
+    if (get_tw1024(ctx, &a.tw)) return 1;
+    return launch_wf1024(ctx, a, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------

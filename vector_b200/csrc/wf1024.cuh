@@ -58,7 +58,7 @@ constexpr size_t kWfSmemBulk = kWfOffZero + 4096;
 
 struct WfArgs {
     PlaceArgs place;             // descriptors + the vector slab [lo, hi) this launch stores; lo = frame_lo * 512
-    float2 *vec;                 // vec[0] = sample place.lo
+    float2 *vec;                 // FUSED: vector out, vec[0] = sample place.lo.  PLAIN: vector in, vec[0] = first sample of frame 0 of this launch
     const unsigned long long *maxsq;
     int mode;                    // B200VEC_BUILD_STORE or B200VEC_BUILD_SCALE
     const float *window;         // 1024 taps
@@ -75,6 +75,7 @@ struct WfArgs {
     long long norm_units;        // 1024-sample units over all ranges (a range's last unit may be partial)
     int n_norm;
     double *maxsq_out;           // receives max |v|^2 (may be NULL)
+    int plain;                   // host side: launch the PLAIN instantiation
     unsigned int *ctr;           // [0] next work item, [1] finished CTAs, [2] grid barrier, [4..5] max |v|^2 bits (all zero between launches)
 };
 
@@ -170,7 +171,10 @@ __device__ __forceinline__ void wf_store_half(float2 *vec, long long s, long lon
 
 // CHUNK = frames per work item.  DBG (timing experiments only, results are wrong when non-zero):
 // bit 0 drops the spectrogram stores, bit 1 the vector stores, bit 2 both transforms.
-template <int CHUNK, int DBG, bool BULK>
+// PLAIN: stand-alone STFT of an existing vector (b200vec_stft1024_fm): halves are read from a.vec
+// (8-byte loads, 256 B per warp instruction, each sample read once per item + one shared half),
+// nothing is placed, scaled or stored back.
+template <int CHUNK, int DBG, bool BULK, bool PLAIN>
 __global__ void __launch_bounds__(kWfThreads, 1)
 wf1024_kernel(const __grid_constant__ WfArgs a) {
     extern __shared__ __align__(16) unsigned char w_smem[];
@@ -201,7 +205,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);        // numpy's complex64 / float32: multiply by the fp32 reciprocal
     }
     __syncthreads();
-    if (a.mode == kWfAutoNorm) {
+    if (!PLAIN && a.mode == kWfAutoNorm) {
         // Pass A inside the kernel (single-GPU builds): every warp evaluates its share of the ranges whose
         // max is the max of the whole vector (hostmath.max_eval_ranges), the grid meets at a barrier
         // (cooperative launch: all CTAs are resident), and everybody reads the same exact max.
@@ -277,7 +281,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         const long long h0 = big ? c * CHUNK : a.n_big * CHUNK + (c - a.n_big);   // its first half-frame / frame (slab-relative)
         // ---------------------------------------------------------------- S
         int cnt_l = 0, rel0_l = 0;
-        if (lane < a.place.np) {
+        if (!PLAIN && lane < a.place.np) {
             const PlaceDesc &d = a.place.d[lane];
             const long long s0 = a.place.lo + h0 * 512;
             long long klo = floor_div(s0 - d.len - d.start, d.period) + 1;
@@ -291,16 +295,30 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         const unsigned active = __ballot_sync(0xffffffffu, cnt_l > 0);
 
         float2 xo[16], xn[16];
-        bool live_o = wf_build_half(a, active, cnt_l, rel0_l, 0, lane, xo);
-        wf_store_half<!(DBG & 2), BULK>(a.vec, h0 * 512, n_vec, live_o, scl, lane, xo, vst, zero_u32);
+        bool live_o = true;
+        if (PLAIN) {
+            const float2 *src = a.vec + h0 * 512 + lane;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) xo[j] = __ldcs(src + 32 * j);
+        } else {
+            live_o = wf_build_half(a, active, cnt_l, rel0_l, 0, lane, xo);
+            wf_store_half<!(DBG & 2), BULK>(a.vec, h0 * 512, n_vec, live_o, scl, lane, xo, vst, zero_u32);
+        }
 #pragma unroll 1
         for (int i = 0; i < cn; ++i) {
             const long long h = h0 + i;
             const bool fv = h < a.n_frames;                                   // frame h exists
-            const bool sv = (i + 1 < cn) && (h + 1) * 512 < n_vec;      // this item stores half h + 1
+            const bool sv = !PLAIN && (i + 1 < cn) && (h + 1) * 512 < n_vec;      // this item stores half h + 1
             if (!fv && !sv) break;
-            const bool live_n = wf_build_half(a, active, cnt_l, rel0_l, (i + 1) * 512, lane, xn);
-            wf_store_half<!(DBG & 2), BULK>(a.vec, sv ? (h + 1) * 512 : n_vec, n_vec, live_n, scl, lane, xn, vst, zero_u32);
+            bool live_n = true;
+            if (PLAIN) {
+                const float2 *src = a.vec + (h + 1) * 512 + lane;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) xn[j] = __ldcs(src + 32 * j);
+            } else {
+                live_n = wf_build_half(a, active, cnt_l, rel0_l, (i + 1) * 512, lane, xn);
+                wf_store_half<!(DBG & 2), BULK>(a.vec, sv ? (h + 1) * 512 : n_vec, n_vec, live_n, scl, lane, xn, vst, zero_u32);
+            }
             if (fv) {
                 float *of = a.out + h * a.out_ld;
                 if (live_o || live_n) {
@@ -366,16 +384,17 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
     }
 }
 
-template <int CHUNK, int DBG, bool BULK>
+template <int CHUNK, int DBG, bool BULK, bool PLAIN = false>
 inline cudaError_t wf1024_attr() {
-    cudaError_t e = cudaFuncSetAttribute(wf1024_kernel<CHUNK, DBG, BULK>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    cudaError_t e = cudaFuncSetAttribute(wf1024_kernel<CHUNK, DBG, BULK, PLAIN>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                          (int)cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(wf1024_kernel<CHUNK, DBG, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    return cudaFuncSetAttribute(wf1024_kernel<CHUNK, DBG, BULK, PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(BULK ? kWfSmemBulk : kWfSmemDirect));
 }
 inline int wf1024_setup() {
     B2_CUDA((wf1024_attr<4, 0, true>())); B2_CUDA((wf1024_attr<8, 0, true>())); B2_CUDA((wf1024_attr<2, 0, true>()));
+    B2_CUDA((wf1024_attr<4, 0, true, true>()));
     B2_CUDA((wf1024_attr<4, 0, false>())); B2_CUDA((wf1024_attr<8, 0, false>())); B2_CUDA((wf1024_attr<2, 0, false>()));
 #ifdef B2_WF_ABLATION
     B2_CUDA((wf1024_attr<4, 1, false>())); B2_CUDA((wf1024_attr<4, 2, false>())); B2_CUDA((wf1024_attr<4, 3, false>()));
@@ -393,7 +412,7 @@ inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
     bool tail = true;
     if (const char *e = getenv("B200VEC_WF_TAIL")) tail = e[0] != '0';      // "0": no single-frame items at the end (A/B)
     B2_REQUIRE(chunk == 2 || chunk == 4 || chunk == 8, "B200VEC_WF_CHUNK must be 2, 4 or 8");
-    const long long n_vec = a.place.hi - a.place.lo;
+    const long long n_vec = a.plain ? 0 : a.place.hi - a.place.lo;
     const long long halves = (n_vec + 511) / 512;
     const long long units = a.n_frames > halves ? a.n_frames : halves;
     // Guided tail: the last ~2 items' worth of frames per warp are handed out one frame at a time, so
@@ -415,13 +434,18 @@ inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
     const unsigned grid = (unsigned)(need < cap ? need : cap);
     // the in-kernel max needs a grid barrier: cooperative launch (all CTAs resident, or the launch fails)
     void *kargs[] = {&a};
+    if (a.plain) {
+        wf1024_kernel<4, 0, true, true><<<grid, kWfThreads, kWfSmemBulk, st>>>(a);
+        B2_CUDA(cudaGetLastError());
+        return 0;
+    }
 #define B2_WF_LAUNCH(C, D, B)                                                                              \
     do {                                                                                                   \
         if (a.mode == kWfAutoNorm)                                                                         \
-            B2_CUDA(cudaLaunchCooperativeKernel((const void *)wf1024_kernel<C, D, B>, dim3(grid), dim3(kWfThreads), \
+            B2_CUDA(cudaLaunchCooperativeKernel((const void *)wf1024_kernel<C, D, B, false>, dim3(grid), dim3(kWfThreads), \
                                                 kargs, (B) ? kWfSmemBulk : kWfSmemDirect, st));            \
         else                                                                                               \
-            wf1024_kernel<C, D, B><<<grid, kWfThreads, (B) ? kWfSmemBulk : kWfSmemDirect, st>>>(a);        \
+            wf1024_kernel<C, D, B, false><<<grid, kWfThreads, (B) ? kWfSmemBulk : kWfSmemDirect, st>>>(a);        \
     } while (0)
     if (dbg == 0) {
         const int sel = (chunk == 8 ? 4 : chunk == 2 ? 2 : 0) | (bulk ? 1 : 0);

@@ -193,21 +193,34 @@ class Engine:
         return torch.empty((nfft, max(pitch, 32)), dtype=torch.float32, device=self.device)[:, :n_frames]
 
     def stft(self, x, window, nperseg, noverlap, nfft, fs, scaling="density", stride=1,
-             in_origin=0, frame_lo=0, n_frames=None, total_len=None, out=None, flag=None):
+             in_origin=0, frame_lo=0, n_frames=None, total_len=None, out=None, flag=None, frame_major=None):
         """|STFT|^2*scale of x[::stride] -> float32 [nfft, n_frames], rows fftshifted.
-        x is a complex64 CUDA tensor whose element 0 is vector sample `in_origin`."""
+        x is a complex64 CUDA tensor whose element 0 is vector sample `in_origin`.
+        The full-rate analysis shape (nperseg = nfft = 1024, hop 512, stride 1) defaults to
+        frame-major memory (the result is the transpose view of a [n_frames, 1024] buffer) and the
+        warp-per-frame kernel; pass frame_major=False (or a C-order `out`) for C-order rows."""
         hop = nperseg - noverlap
         total_len = (in_origin + x.numel()) if total_len is None else total_len
         n_dec = (total_len + stride - 1) // stride
         if n_frames is None:
             n_frames = 0 if n_dec < nperseg else (n_dec - nperseg) // hop + 1 - frame_lo
+        fm_shape = nperseg == 1024 and nfft == 1024 and hop == 512 and stride == 1
         if out is None:
-            out = self.alloc_spectrogram(nfft, max(n_frames, 0))
+            fm = fm_shape if frame_major is None else (frame_major and fm_shape)
+            out = self.alloc_spectrogram(nfft, max(n_frames, 0), frame_major=fm)
         taps, scale = self.window(window, nperseg, fs, scaling)
-        check(self.lib.b200vec_stft(self._ctx, self._ptr(x), int(in_origin), x.numel(), int(stride),
-                                    int(nperseg), int(hop), int(nfft), self._ptr(taps), scale,
-                                    int(frame_lo), int(n_frames), self._ptr(out), out.stride(0),
-                                    self._ptr(flag) if flag is not None else None, self._stream()))
+        fl = self._ptr(flag) if flag is not None else None
+        if fm_shape and out.dim() == 2 and out.stride(0) == 1 and out.stride(1) >= 1024 and n_frames > 0:
+            check(self.lib.b200vec_stft1024_fm(self._ctx, self._ptr(x), int(in_origin), x.numel(), self._ptr(taps),
+                                               scale, int(frame_lo), int(n_frames), self._ptr(out), out.stride(1),
+                                               fl, self._stream()))
+        else:
+            if n_frames > 1 and out.stride(1) != 1:
+                raise ValueError("this STFT shape needs C-order spectrogram memory")
+            check(self.lib.b200vec_stft(self._ctx, self._ptr(x), int(in_origin), x.numel(), int(stride),
+                                        int(nperseg), int(hop), int(nfft), self._ptr(taps), scale,
+                                        int(frame_lo), int(n_frames), self._ptr(out), out.stride(0),
+                                        fl, self._stream()))
         self.launches += 1
         return out
 
