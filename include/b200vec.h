@@ -182,6 +182,12 @@ int b200vec_select_ranks(b200vec_ctx *ctx, const float *data_dev, int64_t n, int
 int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, int16_t *out_dev,
                         void *stream);
 
+/* ---- MAT v5 payload (save_vector, utils.py:659-670 -> scipy.io.savemat) --------------------
+ * MAT v5 stores a complex array as two planes: re_out[i] = Re in[i], im_out[i] = Im in[i]
+ * (float32).  16 B per sample of HBM traffic; all three buffers 16-byte aligned. */
+int b200vec_split_planes(b200vec_ctx *ctx, const void *in_dev, int64_t n, float *re_out_dev,
+                         float *im_out_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -655,3 +655,17 @@ def test_ranged_max_equals_full_max(eng, name, n):
         assert torch.equal(m, full)
     want = O.build_vector(pk, case["configs"], n, False)[0]
     assert abs(np.sqrt(full.item()) - float(np.max(np.abs(want)))) <= 2e-7 * np.sqrt(full.item())   # np.abs is a float32 hypot
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 7, 4097, 560_003])
+def test_save_vector_from_device_matches_host_writer(eng, tmp_path, n):
+    """save_vector(CUDA tensor): device plane split (K7) + pinned D2H writes the same bytes as the host path."""
+    from vector_b200 import api
+    rng = np.random.default_rng(n)
+    v = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+    api.save_vector(v, str(tmp_path / "h.mat"))
+    api.save_vector(torch.from_numpy(v).to(eng.device), str(tmp_path / "d.mat"))
+    h, d = (tmp_path / "h.mat").read_bytes(), (tmp_path / "d.mat").read_bytes()
+    assert len(h) == len(d) and h[128:] == d[128:]
+    y, pre = api.load_packet_info(str(tmp_path / "d.mat"))
+    assert np.array_equal(y, v) and pre == 0

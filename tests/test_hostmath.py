@@ -235,3 +235,38 @@ def test_max_eval_ranges_cfg2_shape():
         p = H.period_samples(per / 1000, 56e6); s = H.start_offset(st / 1000, 100, 56e6)
         rows.append((s, p, H.instance_count(s, p, 56100, 56_000_000), 0))
     assert H.max_eval_ranges(rows, [56100] * 6, 56_000_000) == [(0, 8_344_000), (55_999_900, 56_000_000)]
+
+
+# ------------------------------------------------------------------------------ MAT v5 fast writer
+@pytest.mark.parametrize("n", [0, 1, 2, 3, 5, 6, 1000, 56_101])
+def test_save_vector_matches_savemat_bytes(tmp_path, n):
+    """api.save_vector writes savemat's exact element bytes (utils.py:659-670): everything after the
+    128-byte text header (which carries the time of day) is identical, and load_packet_info reads the
+    file back like the reference's own files."""
+    import io
+    import scipy.io as sio
+    from vector_b200 import api
+    rng = np.random.default_rng(n)
+    v = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+    path = tmp_path / "v.mat"
+    api.save_vector(v, str(path))
+    got = path.read_bytes()
+    ref = io.BytesIO()
+    sio.savemat(ref, {"Y": v, "pre_samples": 0})
+    ref = ref.getvalue()
+    assert len(got) == len(ref) and got[128:] == ref[128:]
+    assert got[116:128] == ref[116:128] and got[:48] == ref[:48]        # version / endian, "MATLAB 5.0 MAT-file Platform: ..."
+    back = sio.loadmat(str(path))
+    assert back["Y"].dtype == np.complex64 and np.array_equal(back["Y"].ravel(), v) and int(back["pre_samples"].item()) == 0
+    if n >= 2:                       # (a 1-sample file squeezes to a Python scalar in the reference's loader too)
+        y, pre = api.load_packet_info(str(path))
+        assert np.array_equal(y, v) and pre == 0
+
+
+def test_save_vector_flattens_and_casts(tmp_path):
+    from vector_b200 import api
+    import scipy.io as sio
+    v = (np.arange(12) - 3j * np.arange(12)).reshape(3, 4).astype(np.complex128)
+    api.save_vector(v, str(tmp_path / "m.mat"))
+    back = sio.loadmat(str(tmp_path / "m.mat"))["Y"]
+    assert back.shape == (1, 12) and back.dtype == np.complex64 and np.array_equal(back.ravel(), v.ravel().astype(np.complex64))

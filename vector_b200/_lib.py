@@ -62,6 +62,7 @@ _SIGNATURES = {
                                        C.POINTER(C.c_int64), C.c_int, C.POINTER(C.c_float),
                                        C.c_void_p]),
     "b200vec_wv_quantize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "b200vec_split_planes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

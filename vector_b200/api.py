@@ -8,6 +8,8 @@ Citations are into the reference.
 from __future__ import annotations
 
 import os
+import struct
+import time
 from datetime import datetime
 
 import numpy as np
@@ -56,12 +58,76 @@ def load_packet(file_path):
         raise
 
 
+def _mat5_tag(mtype, nbytes):
+    return struct.pack("<II", mtype, nbytes)
+
+
+def _mat5_y_header(n):
+    """Everything of the miMATRIX element 'Y' (complex single, 1 x n) up to the real-part data, as
+    scipy.io.savemat lays it out (oned_as='row', no compression) for n >= 2."""
+    plane = 8 + (4 * n + 7) // 8 * 8
+    body = (_mat5_tag(6, 8) + struct.pack("<II", 7 | 0x0800, 0)          # array flags: mxSINGLE_CLASS, complex
+            + _mat5_tag(5, 8) + struct.pack("<ii", 1, n)                  # dimensions
+            + struct.pack("<HH4s", 1, 1, b"Y\0\0\0"))                    # name, small data element
+    return _mat5_tag(14, len(body) + 2 * plane) + body
+
+
+_MAT5_PRE_SAMPLES = (_mat5_tag(14, 0x48) + _mat5_tag(6, 8) + struct.pack("<II", 14, 0)   # mxINT64_CLASS
+                     + _mat5_tag(5, 8) + struct.pack("<ii", 1, 1)
+                     + _mat5_tag(1, 11) + b"pre_samples".ljust(16, b"\0")
+                     + _mat5_tag(12, 8) + struct.pack("<q", 0))
+
+
+def _mat5_file_header():
+    text = ("MATLAB 5.0 MAT-file Platform: %s, Created on: %s" % (os.name, time.asctime())).encode("latin1")
+    return text[:116].ljust(116, b"\0") + b"\0" * 8 + struct.pack("<H", 0x0100) + b"IM"
+
+
+def _write_mat5_vector(output_path, re_plane, im_plane, n):
+    """MAT v5 file {'Y': complex single 1 x n, 'pre_samples': int64 0} written straight from the two
+    float32 planes — byte-identical to scipy.io.savemat's output after the 128-byte text header."""
+    pad = b"\0" * ((-4 * n) % 8)
+    with open(output_path, "wb") as fh:
+        fh.write(_mat5_file_header())
+        fh.write(_mat5_y_header(n))
+        for plane in (re_plane, im_plane):
+            fh.write(_mat5_tag(7, 4 * n))
+            fh.write(memoryview(plane).cast("B"))
+            fh.write(pad)
+        fh.write(_MAT5_PRE_SAMPLES)
+
+
 def save_vector(vector, output_path):
-    """MAT v5 {'Y': complex64 1-D, 'pre_samples': 0} — utils.py:659-670."""
+    """MAT v5 {'Y': complex64 1-D, 'pre_samples': 0} — utils.py:659-670.  `vector` is a numpy array
+    (the reference's argument) or a complex64 CUDA tensor.  The file is written directly in
+    savemat's layout (two float32 planes) instead of through scipy's generic writer; a CUDA tensor is
+    split into its planes on the device (K7) and leaves through pinned memory.  Vectors shorter than
+    2 samples or too long for one MAT v5 element (>= 2^29 samples) go through scipy.io.savemat, which
+    then produces the very output / exception the reference produces."""
+    if isinstance(vector, torch.Tensor) and vector.is_cuda:
+        dev = vector.reshape(-1)
+        if dev.dtype != torch.complex64:
+            dev = dev.to(torch.complex64)
+        n = dev.numel()
+        if 2 <= n < (1 << 29):
+            eng = get_engine(dev.device)
+            planes = eng.split_planes(dev)
+            host = torch.empty(planes.shape, dtype=torch.float32).pin_memory()
+            host.copy_(planes, non_blocking=True)
+            torch.cuda.current_stream(dev.device).synchronize()
+            hp = host.numpy()
+            _write_mat5_vector(output_path, hp[0], hp[1], n)
+            return
+        vector = dev.cpu().numpy()
     vector = np.asarray(vector)
     if vector.ndim > 1:
         vector = vector.flatten()
-    sio.savemat(output_path, {"Y": vector.astype(np.complex64), "pre_samples": 0})
+    vector = vector.astype(np.complex64)
+    n = vector.shape[0]
+    if 2 <= n < (1 << 29):
+        _write_mat5_vector(output_path, np.ascontiguousarray(vector.real), np.ascontiguousarray(vector.imag), n)
+    else:
+        sio.savemat(output_path, {"Y": vector, "pre_samples": 0})
 
 
 def wv_header(n_samples, sample_rate, rms_dbfs=0.0, peak_dbfs=0.0, date=None):

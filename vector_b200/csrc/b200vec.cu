@@ -27,6 +27,24 @@ wv_quantize_kernel(const float2 *__restrict__ in, long long n, short2 *__restric
     }
 }
 
+// K7: complex64 interleaved -> planar float32 real / imaginary parts, the layout MAT v5 stores a
+// complex array in (utils.py:659-670 -> scipy.io.savemat writes the pr and pi sub-elements apart).
+__global__ void __launch_bounds__(256)
+split_planes_kernel(const float2 *__restrict__ in, long long n, float *__restrict__ re, float *__restrict__ im) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long n4 = n / 4;
+    const float4 *in4 = reinterpret_cast<const float4 *>(in);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 a = __ldcs(in4 + 2 * i), b = __ldcs(in4 + 2 * i + 1);
+        __stcs(reinterpret_cast<float4 *>(re) + i, make_float4(a.x, a.z, b.x, b.z));
+        __stcs(reinterpret_cast<float4 *>(im) + i, make_float4(a.y, a.w, b.y, b.w));
+    }
+    for (long long i = 4 * n4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float2 v = in[i];
+        re[i] = v.x; im[i] = v.y;
+    }
+}
+
 __global__ void sel_init(unsigned int *hist, SelState init) {
     *reinterpret_cast<SelState *>(hist + kStateOff) = init;
 }
@@ -510,5 +528,20 @@ int b200vec_debug_pipe_cta(long long *out_host) {
     return cudaMemcpyFromSymbol(out_host, b200vec::g_pipe_cta, sizeof(long long) * 320 * 4) != cudaSuccess;
 }
 #endif
+
+int b200vec_split_planes(b200vec_ctx *ctx, const void *in_dev, int64_t n, float *re_out_dev, float *im_out_dev,
+                         void *stream) {
+    B2_REQUIRE(ctx && n >= 0 && (n == 0 || (in_dev && re_out_dev && im_out_dev)), "NULL argument");
+    B2_REQUIRE((((uintptr_t)in_dev | (uintptr_t)re_out_dev | (uintptr_t)im_out_dev) & 15) == 0,
+               "buffers must be 16-byte aligned");
+    if (n == 0) return 0;
+    DeviceGuard g(ctx->device);
+    long long grid = (n / 4 + 255) / 256 + 1;
+    const long long cap = (long long)ctx->sm_count * 8;
+    if (grid > cap) grid = cap;
+    split_planes_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>((const float2 *)in_dev, n, re_out_dev, im_out_dev);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
 
 }  // extern "C"

@@ -290,6 +290,23 @@ class Engine:
 _ENGINES = {}
 
 
+def _split_planes(self, x, out=None):
+    """complex64 CUDA tensor [n] -> float32 [2, n] (row 0 real, row 1 imaginary): the two planes a
+    MAT v5 complex array is stored as (K7, b200vec_split_planes)."""
+    x = x.reshape(-1)
+    n = x.numel()
+    pitch = (n + 3) // 4 * 4                                  # both rows 16-byte aligned
+    if out is None:
+        out = torch.empty((2, max(pitch, 4)), dtype=torch.float32, device=self.device)
+    check(self.lib.b200vec_split_planes(self._ctx, self._ptr(x), n, self._ptr(out[0]), self._ptr(out[1]),
+                                        self._stream()))
+    self.launches += 1
+    return out[:, :n]
+
+
+Engine.split_planes = _split_planes
+
+
 def get_engine(device=None):
     """Process-wide Engine for `device` (default: torch's current CUDA device)."""
     if not torch.cuda.is_available():
