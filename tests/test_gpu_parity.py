@@ -669,3 +669,67 @@ def test_save_vector_from_device_matches_host_writer(eng, tmp_path, n):
     assert len(h) == len(d) and h[128:] == d[128:]
     y, pre = api.load_packet_info(str(tmp_path / "d.mat"))
     assert np.array_equal(y, v) and pre == 0
+
+
+# ------------------------------------------------------------------------------ cfg4 / cfg5 shapes
+def _cfg4_case(ms):
+    """SURVEY.md §8d cfg4 shortened to `ms` milliseconds: 200 MSa/s, the six packets made at 56 MSa/s and
+    resampled to 200 MSa/s (L' = int(56100*200/56) = 200357, K0), shifts +20/-35/+10/-60/+45/-80 MHz,
+    dense periods 2.0/1.5/1.0/0.8/0.5/0.4 ms (shorter than the 1 ms packets: instances of one packet overlap)."""
+    from vector_b200 import synth
+    fs = 200e6
+    cfgs, pk = synth.scenario(synth.CFG4_ROWS, 56e6)
+    for c in cfgs:
+        c["sample_rate"] = 56e6
+    return fs, cfgs, pk, int(ms * 1e-3 * fs)
+
+
+def test_cfg4_shape_matches_oracle_and_shards(eng):
+    from vector_b200 import dist as vdist, generate
+    from vector_b200._lib import BUILD_MAXONLY, BUILD_SCALE
+    fs, cfgs, pk, n = _cfg4_case(30)                                   # 6 M samples; the trains share a 12 ms period
+    want, _, counts_ref, _ = O.build_vector(pk, cfgs, n, True, fs=fs, resample=True)
+    info = generate.prepare_bank(eng, cfgs, pk, fs, resample=True)
+    assert [i[0] for i in info] == [200357] * 6
+    rows = generate.placement_rows(cfgs, info, n, fs)
+    assert [r[2] for r in rows] == counts_ref
+    plan = vdist.plan_slab(n, 1, 0, 1024, 512, 1, align=512)
+    vec, spec, _ = vdist.build_stft_slab(eng, rows, plan, True, None, fs=fs)          # ONE launch, in-kernel max
+    assert P.rel_l2(vec.cpu().numpy(), want) <= P.VEC_REL_L2
+    _, _, Sr = O.full_rate_spectrogram(want, fs)
+    assert P.spec_db_error(spec.cpu().numpy(), Sr) <= P.SPEC_DB
+    # time-sharded over 2 / 4 / 8 ranks (emulated one after another): pass A shares MAX-combine to the
+    # same double, slabs and spectrogram columns concatenate bit for bit
+    descs, nd = eng.make_descs(rows)
+    for world in (2, 4, 8):
+        plans = [vdist.plan_slab(n, world, r, 1024, 512, 1, align=512) for r in range(world)]
+        maxsq = torch.zeros(1, dtype=torch.float64, device=eng.device)
+        for r in range(world):
+            eng.max_pass(descs, nd, eng.max_ranges(rows, n, world, r), maxsq=maxsq)
+        assert torch.equal(maxsq, eng._maxsq)
+        vecs, specs = [], []
+        for pl in plans:
+            v = torch.empty(pl.hi - pl.lo, dtype=torch.complex64, device=eng.device)
+            sp = eng.alloc_spectrogram(1024, pl.frame_hi - pl.frame_lo, frame_major=True)
+            eng.build_stft1024(descs, nd, pl.lo, pl.hi, v, BUILD_SCALE, pl.frame_lo, pl.frame_hi - pl.frame_lo, sp,
+                               fs=fs, maxsq=maxsq)
+            vecs.append(v); specs.append(sp)
+        assert torch.equal(torch.cat(vecs), vec)
+        assert torch.equal(torch.cat(specs, dim=1), spec)
+
+
+@pytest.mark.parametrize("v", [0, 1, 2, 3, 100, 255])
+def test_cfg5_scenarios_match_oracle(eng, v):
+    """vector v of the 256-vector parameter sweep (3 packets, 100 ms @ 56 MSa/s, shift /
+    period / start drawn from default_rng(5000 + v)); independent vectors, no collective."""
+    from vector_b200 import generate, synth
+    cfgs, pk = synth.scenario(synth.cfg5_rows(v), 56e6)
+    n = 5_600_000
+    want, _, counts_ref, _ = O.build_vector(pk, cfgs, n, True)
+    vec, _, counts, _ = generate.build_vector_device(cfgs, n, True, packets=pk, engine=eng)
+    assert counts == counts_ref
+    assert P.rel_l2(vec.cpu().numpy(), want) <= P.VEC_REL_L2
+    plan, rows, fvec, fspec = _fused(eng, cfgs, pk, n, True)
+    assert torch.equal(fvec, vec)
+    _, _, Sr = O.full_rate_spectrogram(want, 56e6)
+    assert P.spec_db_error(fspec.cpu().numpy(), Sr) <= P.SPEC_DB
