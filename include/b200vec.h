@@ -161,6 +161,22 @@ int b200vec_stft1024_fm(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin,
                         const float *window_dev, float scale, int64_t frame_lo, int64_t n_frames,
                         float *out_dev, int64_t out_ld, int *nonzero_flag_dev, void *stream);
 
+/* The multi-GPU form of b200vec_build_stft1024_fm_norm: still ONE launch per GPU and step, and the
+ * path's only collective — MAX of one double — runs INSIDE the kernel over NVLink peer memory
+ * instead of as a separate NCCL all-reduce between two launches.  Every rank passes its share of the
+ * norm ranges and the same `epoch` (1, 2, 3, ... one per step).  peer_blocks[r] is rank r's 64-byte,
+ * zero-initialised, symmetric block mapped into this process (torch symmetric memory, cuMem or
+ * cudaIpc): u64[0..1] max slots for even / odd epochs, u32 at byte 16 the arrival counter.  CTA 0
+ * raises every GPU's slot with the local max (system-scope atomicMax), signals every GPU and waits
+ * for `world` arrivals at home; all ranks then scale by the same exact max.  world <= 8. */
+int b200vec_build_stft1024_fm_norm_peer(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                                        int64_t slab_lo, int64_t slab_hi, void *vec_out_dev,
+                                        const int64_t *norm_ranges, int n_ranges,
+                                        void *const *peer_blocks, int world, int rank, uint32_t epoch,
+                                        double *maxsq_dev, const float *window_dev, float scale,
+                                        int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                                        int *nonzero_flag_dev, void *stream);
+
 /* ---- dB map and order statistics (normalize_spectrogram, utils.py:356-404) -----------
  * db      : out[i] = 10*log10(|s[i]| + floor)                      (utils.py:363-368)
  * select  : exact order statistics of a float32 array: ranks[] are 0-based positions in the

@@ -733,3 +733,24 @@ def test_cfg5_scenarios_match_oracle(eng, v):
     assert torch.equal(fvec, vec)
     _, _, Sr = O.full_rate_spectrogram(want, 56e6)
     assert P.spec_db_error(fspec.cpu().numpy(), Sr) <= P.SPEC_DB
+
+
+def test_peer_max_protocol_single_rank(eng):
+    """b200vec_build_stft1024_fm_norm_peer with world = 1 (the block is local memory): the epoch /
+    slot-parity / arrival protocol runs for several steps and gives the in-kernel-max result every time."""
+    from vector_b200 import dist as vdist, generate
+    case = cases.build_cases()["cfg1_100ms"]
+    pk = O.packets_for(case["configs"])
+    n = 1_000_000
+    info = generate.prepare_bank(eng, case["configs"], pk, 56e6)
+    rows = generate.placement_rows(case["configs"], info, n, 56e6)
+    plan = vdist.plan_slab(n, 1, 0, 1024, 512, 1, align=512)
+    vec0, spec0, m0 = vdist.build_stft_slab(eng, rows, plan, True, None, fs=56e6)
+    m0 = m0.clone()
+    block = torch.zeros(16, dtype=torch.int32, device=eng.device)
+    peer = vdist.PeerMax(blocks=([block.data_ptr()], 1, 0))
+    for step in range(1, 5):
+        vec, spec, m = vdist.build_stft_slab(eng, rows, plan, True, None, fs=56e6, peer=peer)
+        assert peer.epoch == step
+        assert torch.equal(m, m0) and torch.equal(vec, vec0) and torch.equal(spec, spec0)
+    assert int(block[4]) == 4                                           # one arrival per epoch

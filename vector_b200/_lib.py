@@ -55,6 +55,11 @@ _SIGNATURES = {
                                                  C.c_int64, C.c_void_p, C.c_void_p]),
     "b200vec_stft1024_fm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_float,
                                       C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "b200vec_build_stft1024_fm_norm_peer": (C.c_int, [C.c_void_p, C.POINTER(PktDesc), C.c_int, C.c_int64, C.c_int64,
+                                                      C.c_void_p, C.POINTER(C.c_int64), C.c_int,
+                                                      C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_uint32, C.c_void_p,
+                                                      C.c_void_p, C.c_float, C.c_int64, C.c_int64, C.c_void_p,
+                                                      C.c_int64, C.c_void_p, C.c_void_p]),
     "b200vec_db": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]),
     "b200vec_select_count": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int,
                                        C.POINTER(C.c_int64), C.c_void_p]),

@@ -374,6 +374,7 @@ int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
 static int build_stft1024_fm_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
                                   int64_t slab_lo, int64_t slab_hi, void *vec_out_dev, int mode,
                                   const int64_t *norm_ranges, int n_ranges,
+                                  void *const *peer_blocks, int world, int rank, unsigned int epoch,
                                   double *maxsq_dev, const float *window_dev, float scale,
                                   int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
                                   int *nonzero_flag_dev, void *stream) {
@@ -381,7 +382,8 @@ static int build_stft1024_fm_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *desc
     B2_REQUIRE(n_pkts >= 0 && n_pkts <= B200VEC_MAX_PACKETS, "too many packets");
     B2_REQUIRE(n_pkts == 0 || descs, "descs is NULL");
     B2_REQUIRE(slab_lo >= 0 && slab_hi >= slab_lo, "bad slab");
-    B2_REQUIRE(mode == B200VEC_BUILD_STORE || mode == B200VEC_BUILD_SCALE || mode == kWfAutoNorm, "bad mode");
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || mode == B200VEC_BUILD_SCALE || mode == kWfAutoNorm ||
+               mode == kWfAutoNormPeer, "bad mode");
     B2_REQUIRE(mode != B200VEC_BUILD_SCALE || maxsq_dev, "maxsq_dev is NULL");
     B2_REQUIRE(vec_out_dev || slab_hi == slab_lo, "vec_out_dev is NULL");
     B2_REQUIRE(((uintptr_t)vec_out_dev & 15) == 0, "vec_out_dev must be 16-byte aligned");
@@ -394,7 +396,18 @@ static int build_stft1024_fm_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *desc
     WfArgs a;
     if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place)) return 1;
     a.n_norm = 0; a.norm_units = 0; a.maxsq_out = nullptr; a.plain = 0;
-    if (mode == kWfAutoNorm) {
+    a.world = 1; a.rank = 0; a.epoch = 0;
+    for (int r = 0; r < kWfMaxPeers; ++r) a.peer[r] = nullptr;
+    if (mode == kWfAutoNormPeer) {
+        B2_REQUIRE(peer_blocks && world >= 1 && world <= kWfMaxPeers && rank >= 0 && rank < world && epoch >= 1,
+                   "bad peer arguments");
+        for (int r = 0; r < world; ++r) {
+            B2_REQUIRE(peer_blocks[r] && ((uintptr_t)peer_blocks[r] & 15) == 0, "peer block NULL or misaligned");
+            a.peer[r] = (unsigned long long *)peer_blocks[r];
+        }
+        a.world = world; a.rank = rank; a.epoch = epoch;
+    }
+    if (mode == kWfAutoNorm || mode == kWfAutoNormPeer) {
         B2_REQUIRE(n_ranges >= 0 && n_ranges <= kWfMaxNormRanges && (n_ranges == 0 || norm_ranges), "bad norm ranges");
         for (int r = 0; r < n_ranges; ++r) {
             const int64_t lo = norm_ranges[2 * r], hi = norm_ranges[2 * r + 1];
@@ -422,8 +435,8 @@ int b200vec_build_stft1024_fm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, i
                               int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
                               int *nonzero_flag_dev, void *stream) {
     B2_REQUIRE(mode == B200VEC_BUILD_STORE || mode == B200VEC_BUILD_SCALE, "mode must be STORE or SCALE");
-    return build_stft1024_fm_impl(ctx, descs, n_pkts, slab_lo, slab_hi, vec_out_dev, mode, nullptr, 0, maxsq_dev,
-                                  window_dev, scale, frame_lo, n_frames, spec_out_dev, out_ld, nonzero_flag_dev, stream);
+    return build_stft1024_fm_impl(ctx, descs, n_pkts, slab_lo, slab_hi, vec_out_dev, mode, nullptr, 0,
+                                  nullptr, 1, 0, 0, maxsq_dev, window_dev, scale, frame_lo, n_frames, spec_out_dev, out_ld, nonzero_flag_dev, stream);
 }
 
 int b200vec_build_stft1024_fm_norm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
@@ -433,8 +446,20 @@ int b200vec_build_stft1024_fm_norm(b200vec_ctx *ctx, const b200vec_pkt_desc *des
                                    int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
                                    int *nonzero_flag_dev, void *stream) {
     return build_stft1024_fm_impl(ctx, descs, n_pkts, slab_lo, slab_hi, vec_out_dev, kWfAutoNorm, norm_ranges, n_ranges,
-                                  maxsq_dev, window_dev, scale, frame_lo, n_frames, spec_out_dev, out_ld,
-                                  nonzero_flag_dev, stream);
+                                  nullptr, 1, 0, 0, maxsq_dev, window_dev, scale, frame_lo, n_frames, spec_out_dev,
+                                  out_ld, nonzero_flag_dev, stream);
+}
+
+int b200vec_build_stft1024_fm_norm_peer(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                                        int64_t slab_lo, int64_t slab_hi, void *vec_out_dev,
+                                        const int64_t *norm_ranges, int n_ranges,
+                                        void *const *peer_blocks, int world, int rank, uint32_t epoch,
+                                        double *maxsq_dev, const float *window_dev, float scale,
+                                        int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
+                                        int *nonzero_flag_dev, void *stream) {
+    return build_stft1024_fm_impl(ctx, descs, n_pkts, slab_lo, slab_hi, vec_out_dev, kWfAutoNormPeer, norm_ranges,
+                                  n_ranges, peer_blocks, world, rank, epoch, maxsq_dev, window_dev, scale, frame_lo,
+                                  n_frames, spec_out_dev, out_ld, nonzero_flag_dev, stream);
 }
 
 int b200vec_stft1024_fm(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_t in_len,

@@ -46,6 +46,8 @@ constexpr int kWfThreads = 32 * kWfWarps;
 constexpr int kWfChunk = 4;                                       // frames per work item (default; B200VEC_WF_CHUNK=4|8 for A/B: 190 vs 203 us)
 constexpr int kWfMaxNormRanges = 4;
 constexpr int kWfAutoNorm = 3;                                    // WfArgs::mode: find the max in-kernel, then scale
+constexpr int kWfAutoNormPeer = 4;                                // same, and MAX-combine it with the other GPUs through peer memory
+constexpr int kWfMaxPeers = 8;
 constexpr int kWfExPitch = 33;                                    // float2 per l-row of a warp's exchange block
 constexpr size_t kWfOffExch = 0;
 constexpr size_t kWfOffTw = kWfOffExch + (size_t)kWfWarps * 32 * kWfExPitch * sizeof(float2);
@@ -76,7 +78,12 @@ struct WfArgs {
     int n_norm;
     double *maxsq_out;           // receives max |v|^2 (may be NULL)
     int plain;                   // host side: launch the PLAIN instantiation
-    unsigned int *ctr;           // [0] next work item, [1] finished CTAs, [2] grid barrier, [4..5] max |v|^2 bits (all zero between launches)
+    // kWfAutoNormPeer: one symmetric 64-byte block per GPU, peer[r] = rank r's block mapped here:
+    //   u64 [0], [1]  max |v|^2 bits of even / odd epochs      u32 at byte 16: arrivals (monotonic)
+    unsigned long long *peer[kWfMaxPeers];
+    int world, rank;
+    unsigned int epoch;          // 1, 2, 3, ... identical on every rank for the same step
+    unsigned int *ctr;           // [0] next work item, [1] finished CTAs, [2] grid barrier, [4..5] max |v|^2 bits (all zero between launches); [3] epoch published, [6..7] combined max (peer mode)
 };
 
 // B: the 512 samples starting `off` samples into the item's span.  Returns false when no packet
@@ -205,7 +212,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);        // numpy's complex64 / float32: multiply by the fp32 reciprocal
     }
     __syncthreads();
-    if (!PLAIN && a.mode == kWfAutoNorm) {
+    if (!PLAIN && (a.mode == kWfAutoNorm || a.mode == kWfAutoNormPeer)) {
         // Pass A inside the kernel (single-GPU builds): every warp evaluates its share of the ranges whose
         // max is the max of the whole vector (hostmath.max_eval_ranges), the grid meets at a barrier
         // (cooperative launch: all CTAs are resident), and everybody reads the same exact max.
@@ -258,6 +265,39 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
             __threadfence();
         }
         __syncthreads();
+        if (a.mode == kWfAutoNormPeer) {
+            // The one collective of the path, inside the kernel: CTA 0 raises every GPU's max slot with this
+            // GPU's max (system-scope atomics over NVLink peer memory), signals its arrival to every GPU and
+            // waits for all `world` arrivals at home; the other CTAs wait for the combined value it publishes.
+            // Slots alternate with the epoch's parity; a slot is cleared one epoch before it is used again,
+            // ahead of the arrival signal that lets any peer start that epoch.
+            unsigned long long *fin = reinterpret_cast<unsigned long long *>(a.ctr + 6);
+            if (blockIdx.x == 0 && tid == 0) {
+                const unsigned long long mine = *reinterpret_cast<volatile unsigned long long *>(slot);
+                unsigned long long *home = a.peer[a.rank];
+                const int cur = a.epoch & 1;
+                home[cur ^ 1] = 0ull;
+                __threadfence_system();
+                for (int r = 0; r < a.world; ++r)
+                    if (mine) atomicMax_system(a.peer[r] + cur, mine);
+                __threadfence_system();
+                for (int r = 0; r < a.world; ++r)
+                    atomicAdd_system(reinterpret_cast<unsigned int *>(a.peer[r] + 2), 1u);
+                volatile unsigned int *arr = reinterpret_cast<volatile unsigned int *>(home + 2);
+                const unsigned int want = a.epoch * (unsigned)a.world;
+                while ((int)(*arr - want) < 0) __nanosleep(100);
+                __threadfence_system();
+                *fin = *reinterpret_cast<volatile unsigned long long *>(home + cur);
+                __threadfence();
+                atomicExch(a.ctr + 3, a.epoch);
+            }
+            if (tid == 0) {
+                while (*reinterpret_cast<volatile unsigned int *>(a.ctr + 3) != a.epoch) __nanosleep(40);
+                __threadfence();
+            }
+            __syncthreads();
+            slot = fin;
+        }
         const double m2 = __longlong_as_double((long long)*reinterpret_cast<volatile unsigned long long *>(slot));
         if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);
         if (blockIdx.x == 0 && tid == 0 && a.maxsq_out) *a.maxsq_out = m2;
@@ -425,8 +465,8 @@ inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
     if (a.n_chunks == 0) return 0;
     B2_REQUIRE(a.n_chunks < 0x7fffffffLL, "slab too long for one launch (split it)");
     if (!ctx->wf_ctr) {
-        B2_CUDA(cudaMalloc(&ctx->wf_ctr, 8 * sizeof(unsigned int)));
-        B2_CUDA(cudaMemsetAsync(ctx->wf_ctr, 0, 8 * sizeof(unsigned int), st));
+        B2_CUDA(cudaMalloc(&ctx->wf_ctr, 16 * sizeof(unsigned int)));
+        B2_CUDA(cudaMemsetAsync(ctx->wf_ctr, 0, 16 * sizeof(unsigned int), st));
     }
     a.ctr = ctx->wf_ctr;
     const long long cap = ctx->sm_count;
@@ -441,7 +481,7 @@ inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
     }
 #define B2_WF_LAUNCH(C, D, B)                                                                              \
     do {                                                                                                   \
-        if (a.mode == kWfAutoNorm)                                                                         \
+        if (a.mode == kWfAutoNorm || a.mode == kWfAutoNormPeer)                                            \
             B2_CUDA(cudaLaunchCooperativeKernel((const void *)wf1024_kernel<C, D, B, false>, dim3(grid), dim3(kWfThreads), \
                                                 kargs, (B) ? kWfSmemBulk : kWfSmemDirect, st));            \
         else                                                                                               \

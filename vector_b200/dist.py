@@ -48,6 +48,37 @@ def make_max_reducer(group=None):
     return reduce_max
 
 
+class PeerMax:
+    """The 64-byte symmetric blocks of the in-kernel MAX exchange (b200vec_build_stft1024_fm_norm_peer):
+    one per rank, allocated with torch symmetric memory so that every rank holds a mapping of every
+    other rank's block (NVLink peer memory).  One epoch per fused step, the same on every rank."""
+
+    def __init__(self, group=None, blocks=None):
+        import torch
+        if blocks is not None:                     # tests: explicit (ptrs, world, rank), e.g. one local block
+            self.ptrs, self.world, self.rank = blocks
+            self.epoch = 0
+            return
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        grp = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(grp), dist.get_rank(grp)
+        if self.world > 8:
+            raise ValueError("PeerMax supports up to 8 ranks (one NVSwitch domain)")
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.buf = symm.empty(16, dtype=torch.int32, device=dev)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, grp)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.epoch = 0
+        torch.cuda.synchronize()
+        dist.barrier(grp)                          # every block is zero before any kernel touches a peer
+
+    def next_epoch(self):
+        self.epoch += 1
+        return self.epoch
+
+
 def build_slab(engine, rows, plan, normalize=True, reduce_max=None, out=None):
     """Owned slab plus halo of the (optionally normalised) vector on this rank's GPU.
     The max pass covers this rank's share of hostmath.max_eval_ranges (one common period of the
@@ -80,7 +111,7 @@ def stft_slab(engine, vec, plan, window="hann", nperseg=1024, noverlap=512, nfft
 
 
 def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6, window="hann",
-                    scaling="density", out_vec=None, out_spec=None):
+                    scaling="density", out_vec=None, out_spec=None, peer=None):
     """Owned slab of the vector AND this rank's spectrogram columns (hann-1024/512 analysis STFT of
     vector_analyzer/spectrogram_analysis.py:35-49) with the fused kernel: pass A (max, no stores)
     -> [all-reduce MAX] -> one kernel that places, scales, stores the vector and transforms it
@@ -100,7 +131,13 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
     descs, nd = engine.make_descs(rows)
     mode, norm_ranges = BUILD_STORE, None
     frame_major = out_spec.dim() == 2 and out_spec.stride(0) == 1 and out_spec.stride(1) >= 1024
-    if normalize and plan.world == 1 and reduce_max is None and frame_major:
+    if normalize and peer is not None and frame_major:
+        # multi-GPU, ONE launch per rank: this rank's share of pass A and the MAX exchange over NVLink
+        # peer memory both run inside the fused kernel (no NCCL call in the step)
+        norm_ranges = engine.max_ranges(rows, plan.total, plan.world, plan.rank)
+        if len(norm_ranges) > 4:
+            raise ValueError("too many max ranges for one launch")
+    elif normalize and plan.world == 1 and reduce_max is None and frame_major:
         # single GPU: pass A runs inside the fused kernel (grid barrier), ONE launch for the step
         norm_ranges = engine.max_ranges(rows, plan.total, 1, 0)
         if len(norm_ranges) > 4:
@@ -112,5 +149,6 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
             reduce_max(engine._maxsq)
         mode = BUILD_SCALE
     engine.build_stft1024(descs, nd, plan.lo, plan.hi, out_vec, mode, frame_lo, nf, out_spec,
-                          window=window, fs=fs, scaling=scaling, norm_ranges=norm_ranges)
+                          window=window, fs=fs, scaling=scaling, norm_ranges=norm_ranges,
+                          peer=peer if norm_ranges is not None else None)
     return out_vec, out_spec, (engine._maxsq if normalize else None)

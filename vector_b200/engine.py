@@ -142,7 +142,7 @@ class Engine:
 
     def build_stft1024(self, descs, n_descs, lo, hi, vec_out, mode, frame_lo, n_frames, spec_out,
                        window="hann", fs=H.TARGET_SAMPLE_RATE, scaling="density", maxsq=None, flag=None,
-                       norm_ranges=None):
+                       norm_ranges=None, peer=None):
         """Fused pass B + full-rate STFT (nperseg = nfft = 1024, hop 512): samples [lo, hi) of the
         vector into vec_out, frames [frame_lo, frame_lo+n_frames) into spec_out, one kernel, the
         vector never re-read.  lo must equal frame_lo*512.  spec_out is a float32 [1024, n_frames]
@@ -151,7 +151,9 @@ class Engine:
         (b200vec_build_stft1024_fm), row-major memory the 16-frame tile kernel.
         norm_ranges (frame-major only): [(lo, hi), ...] sample ranges whose max |v| is the max of the
         whole vector (max_ranges()) — the kernel then finds the max itself, scales by it and writes
-        max |v|^2 to maxsq: the whole normalised step in ONE launch (`mode` is ignored)."""
+        max |v|^2 to maxsq: the whole normalised step in ONE launch (`mode` is ignored).
+        peer (with norm_ranges = this rank's share): a dist.PeerMax — the per-rank maxima are then
+        MAX-combined inside the kernel over NVLink peer memory (no NCCL call in the step)."""
         maxsq = self._maxsq if maxsq is None else maxsq
         taps, scale = self.window(window, 1024, fs, scaling)
         frame_major = spec_out.dim() == 2 and spec_out.stride(0) == 1 and spec_out.stride(1) >= 1024
@@ -162,10 +164,18 @@ class Engine:
                 raise ValueError("in-kernel normalisation needs frame-major spectrogram memory")
             flat = [int(v) for r in norm_ranges for v in r]
             arr = (C.c_int64 * max(len(flat), 1))(*flat)
-            check(self.lib.b200vec_build_stft1024_fm_norm(
-                self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), arr, len(flat) // 2,
-                self._ptr(maxsq), self._ptr(taps), scale, int(frame_lo), int(n_frames), self._ptr(spec_out),
-                ld, fl, self._stream()))
+            if peer is not None:
+                blocks = (C.c_void_p * peer.world)(*peer.ptrs)
+                check(self.lib.b200vec_build_stft1024_fm_norm_peer(
+                    self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), arr, len(flat) // 2,
+                    blocks, peer.world, peer.rank, peer.next_epoch(),
+                    self._ptr(maxsq), self._ptr(taps), scale, int(frame_lo), int(n_frames), self._ptr(spec_out),
+                    ld, fl, self._stream()))
+            else:
+                check(self.lib.b200vec_build_stft1024_fm_norm(
+                    self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), arr, len(flat) // 2,
+                    self._ptr(maxsq), self._ptr(taps), scale, int(frame_lo), int(n_frames), self._ptr(spec_out),
+                    ld, fl, self._stream()))
         else:
             fn = self.lib.b200vec_build_stft1024_fm if frame_major else self.lib.b200vec_build_stft1024
             check(fn(self._ctx, descs, n_descs, int(lo), int(hi), self._ptr(vec_out), mode, self._ptr(maxsq),
