@@ -139,6 +139,10 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly one JSON line: libraries that print there (the NCCL version banner) go to stderr
+    sys.stdout.flush()
+    json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local)
     if world > 1:
@@ -204,7 +208,7 @@ def run_ours(args):
     # CUDA graph so that the timed loop replays device work back to back (no Python / launch gaps).
     graph = None
     launches_per_step = None
-    if not args.no_graph and world == 1:       # N > 1: eager (an NCCL all-reduce inside a captured step hung on this stack)
+    if not args.no_graph and (world == 1 or peer is not None):   # the NCCL form stays eager (an all-reduce inside a captured step hung on this stack)
         try:
             l0 = eng.launches
             side = torch.cuda.Stream()
@@ -335,7 +339,7 @@ def run_ours(args):
         }
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=json_out, flush=True)
     if world > 1:
         dist.destroy_process_group()
 

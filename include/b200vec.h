@@ -164,7 +164,9 @@ int b200vec_stft1024_fm(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin,
 /* The multi-GPU form of b200vec_build_stft1024_fm_norm: still ONE launch per GPU and step, and the
  * path's only collective — MAX of one double — runs INSIDE the kernel over NVLink peer memory
  * instead of as a separate NCCL all-reduce between two launches.  Every rank passes its share of the
- * norm ranges and the same `epoch` (1, 2, 3, ... one per step).  peer_blocks[r] is rank r's 64-byte,
+ * norm ranges and the same `epoch` (1, 2, 3, ... one per step; 0 = count the steps on the device, in
+ * the u32 at byte 24 of the home block — a step can then be replayed from a CUDA graph).
+ * peer_blocks[r] is rank r's 64-byte,
  * zero-initialised, symmetric block mapped into this process (torch symmetric memory, cuMem or
  * cudaIpc): u64[0..1] max slots for even / odd epochs, u32 at byte 16 the arrival counter.  CTA 0
  * raises every GPU's slot with the local max (system-scope atomicMax), signals every GPU and waits

@@ -399,7 +399,7 @@ static int build_stft1024_fm_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *desc
     a.world = 1; a.rank = 0; a.epoch = 0;
     for (int r = 0; r < kWfMaxPeers; ++r) a.peer[r] = nullptr;
     if (mode == kWfAutoNormPeer) {
-        B2_REQUIRE(peer_blocks && world >= 1 && world <= kWfMaxPeers && rank >= 0 && rank < world && epoch >= 1,
+        B2_REQUIRE(peer_blocks && world >= 1 && world <= kWfMaxPeers && rank >= 0 && rank < world,
                    "bad peer arguments");
         for (int r = 0; r < world; ++r) {
             B2_REQUIRE(peer_blocks[r] && ((uintptr_t)peer_blocks[r] & 15) == 0, "peer block NULL or misaligned");

@@ -82,7 +82,8 @@ struct WfArgs {
     //   u64 [0], [1]  max |v|^2 bits of even / odd epochs      u32 at byte 16: arrivals (monotonic)
     unsigned long long *peer[kWfMaxPeers];
     int world, rank;
-    unsigned int epoch;          // 1, 2, 3, ... identical on every rank for the same step
+    unsigned int epoch;          // 1, 2, 3, ... identical on every rank for the same step; 0: count steps on the device
+                                 // (u32 at byte 24 of the home block), which lets a step be replayed from a CUDA graph
     unsigned int *ctr;           // [0] next work item, [1] finished CTAs, [2] grid barrier, [4..5] max |v|^2 bits (all zero between launches); [3] epoch published, [6..7] combined max (peer mode)
 };
 
@@ -272,10 +273,11 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
             // Slots alternate with the epoch's parity; a slot is cleared one epoch before it is used again,
             // ahead of the arrival signal that lets any peer start that epoch.
             unsigned long long *fin = reinterpret_cast<unsigned long long *>(a.ctr + 6);
+            unsigned long long *home = a.peer[a.rank];
+            const unsigned int epoch = a.epoch ? a.epoch : *reinterpret_cast<volatile unsigned int *>(home + 3) + 1u;
             if (blockIdx.x == 0 && tid == 0) {
                 const unsigned long long mine = *reinterpret_cast<volatile unsigned long long *>(slot);
-                unsigned long long *home = a.peer[a.rank];
-                const int cur = a.epoch & 1;
+                const int cur = epoch & 1;
                 home[cur ^ 1] = 0ull;
                 __threadfence_system();
                 for (int r = 0; r < a.world; ++r)
@@ -284,15 +286,15 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                 for (int r = 0; r < a.world; ++r)
                     atomicAdd_system(reinterpret_cast<unsigned int *>(a.peer[r] + 2), 1u);
                 volatile unsigned int *arr = reinterpret_cast<volatile unsigned int *>(home + 2);
-                const unsigned int want = a.epoch * (unsigned)a.world;
+                const unsigned int want = epoch * (unsigned)a.world;
                 while ((int)(*arr - want) < 0) __nanosleep(100);
                 __threadfence_system();
                 *fin = *reinterpret_cast<volatile unsigned long long *>(home + cur);
                 __threadfence();
-                atomicExch(a.ctr + 3, a.epoch);
+                atomicExch(a.ctr + 3, epoch);
             }
             if (tid == 0) {
-                while (*reinterpret_cast<volatile unsigned int *>(a.ctr + 3) != a.epoch) __nanosleep(40);
+                while (*reinterpret_cast<volatile unsigned int *>(a.ctr + 3) != epoch) __nanosleep(40);
                 __threadfence();
             }
             __syncthreads();
@@ -420,7 +422,12 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
     if (tid == 0) {                                          // the last CTA out re-arms the counters for the next launch
         __threadfence();
         const unsigned done = atomicAdd(a.ctr + 1, 1u);
-        if (done == gridDim.x - 1) { a.ctr[0] = 0; a.ctr[1] = 0; a.ctr[2] = 0; a.ctr[4] = 0; a.ctr[5] = 0; __threadfence(); }
+        if (done == gridDim.x - 1) {
+            a.ctr[0] = 0; a.ctr[1] = 0; a.ctr[2] = 0; a.ctr[4] = 0; a.ctr[5] = 0;
+            if (!PLAIN && a.mode == kWfAutoNormPeer && a.epoch == 0)            // every CTA has read the old count by now
+                *reinterpret_cast<unsigned int *>(a.peer[a.rank] + 3) = a.ctr[3];
+            __threadfence();
+        }
     }
 }
 

@@ -75,8 +75,10 @@ class PeerMax:
         dist.barrier(grp)                          # every block is zero before any kernel touches a peer
 
     def next_epoch(self):
+        """Host-side step count (informational).  The kernel is passed epoch 0 = "count on the device"
+        (u32 at byte 24 of the home block), so a captured step can be replayed from a CUDA graph."""
         self.epoch += 1
-        return self.epoch
+        return 0
 
 
 def build_slab(engine, rows, plan, normalize=True, reduce_max=None, out=None):
