@@ -198,7 +198,12 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         wf_fence_async();
     }
 
-    for (int i = tid; i < 1024; i += kWfThreads) tw[i] = __ldg(a.tw + i);
+    // twiddle pairs in the order the first stage of T2 consumes them: tw4[P][q] = (W^(q la), W^(q lb)),
+    // la = brev5(2 P), lb = brev5(2 P + 1): one 16-byte load per butterfly
+    for (int i = tid; i < 1024; i += kWfThreads) {
+        const int q = i & 31, k = i >> 5;                    // k = 2 P + c
+        tw[(k >> 1) * 64 + q * 2 + (k & 1)] = __ldg(a.tw + brev5(k) * 32 + q);
+    }
     {
         const float rs = sqrtf(a.scale);                    // |X|^2 * scale = |FFT(x * w * sqrt(scale))|^2
         float *wf = reinterpret_cast<float *>(win4);
@@ -307,10 +312,11 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
 
     const long long n_vec = a.place.hi - a.place.lo;
     const float4 *wl = win4 + lane;
-    const float2 *tq = tw + lane;
+    const float4 *tq4 = reinterpret_cast<const float4 *>(tw) + lane;
     float2 *ex_w = exch + lane * kWfExPitch;                 // T1 writes row l = lane
     const float2 *ex_r = exch + lane;                        // T2 reads column q = lane
     unsigned anybits = 0;
+    const bool track = a.flag != nullptr;
 
     unsigned next = 0;
     if (lane == 0) next = atomicAdd(a.ctr, 1u);
@@ -387,14 +393,14 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                         v[brev5(l)].x = s.x; v[brev5(l)].y = s.y;
                     }
                     __syncwarp();                            // the block may be overwritten by the next frame
-                    if (!(DBG & 4)) fft32_twiddled(v, [tq](int l) { const float2 w = tq[32 * l]; return cf32{w.x, w.y}; });
+                    if (!(DBG & 4)) fft32_twiddled_pairs(v, [tq4](int P) { const float4 w = tq4[32 * P]; return cf32x2{w.x, w.y, w.z, w.w}; });
                     // BULK: the frame's 4 KB are staged in the (now free) exchange block and leave as one bulk copy
                     float *o = BULK ? reinterpret_cast<float *>(exch) + lane : of + lane;
 #pragma unroll
                     for (int sp = 0; sp < 32; ++sp) {        // row q + 32 sp holds bin q + 32 s, s = (sp + 16) & 31
                         const int s = (sp + 16) & 31;
                         const float p = b2_fma(v[s].x, v[s].x, v[s].y * v[s].y);
-                        anybits |= __float_as_uint(p);       // p >= 0 or NaN: non-zero bits <=> p != 0
+                        if (track) anybits |= __float_as_uint(p);   // p >= 0 or NaN: non-zero bits <=> p != 0
                         if (BULK) o[32 * sp] = p;
                         else if (!(DBG & 1)) __stcs(o + 32 * sp, p);
                     }
