@@ -206,6 +206,23 @@ int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, int16_t
 int b200vec_split_planes(b200vec_ctx *ctx, const void *in_dev, int64_t n, float *re_out_dev,
                          float *im_out_dev, void *stream);
 
+/* ---- the steps either side of the path -------------------------
+ * box_energy        : detect_packet_bounds' smoothing (utils.py:813-816): smoothed[i] =
+ *                     np.convolve(np.abs(x)**2, np.ones(window)/window, 'same')[i] in float64, and
+ *                     *max_out_dev = smoothed.max().  window <= 1024 (the reference uses fs // 1e6).
+ * threshold_bounds  : first_last_host[0/1] = first / last i with smoothed[i] >= threshold
+ *                     (utils.py:820-825); (n, -1) when none.  Synchronises the stream.
+ * median2_rows      : scipy.ndimage.median_filter(S, size=(2, 1)) as plot_spectrogram applies it to
+ *                     the dB map (utils.py:435-440): out[r][c] = max(S[r-1][c], S[r][c]), row 0 kept.
+ *                     Element strides are explicit so both spectrogram layouts work; not in place. */
+int b200vec_box_energy(b200vec_ctx *ctx, const void *in_dev, int64_t n, int window, double *smoothed_out_dev,
+                       double *max_out_dev, void *stream);
+int b200vec_threshold_bounds(b200vec_ctx *ctx, const double *smoothed_dev, int64_t n, double threshold,
+                             int64_t *first_last_host, void *stream);
+int b200vec_median2_rows(b200vec_ctx *ctx, const float *in_dev, int64_t rows, int64_t cols, int64_t in_row_stride,
+                         int64_t in_col_stride, float *out_dev, int64_t out_row_stride, int64_t out_col_stride,
+                         void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -754,3 +754,50 @@ def test_peer_max_protocol_single_rank(eng):
         assert peer.epoch == step
         assert torch.equal(m, m0) and torch.equal(vec, vec0) and torch.equal(spec, spec0)
     assert int(block[4]) == 4                                           # one arrival per epoch
+
+
+# ------------------------------------------------------------------------------ either side of the path (§8f rank 4)
+@pytest.mark.parametrize("kind,ratio", [("tone", 0.2), ("chirp", 0.2), ("bpsk", 0.2), ("noise", 0.2), ("multitone", 0.5),
+                                        ("tone", 0.05)])
+def test_detect_packet_bounds_matches_reference_statement(eng, kind, ratio):
+    """utils.detect_packet_bounds: packet embedded in a noise floor, indices exact."""
+    import vector_b200 as vb
+    rng = np.random.default_rng(7)
+    body = O.synth_packet(kind, body_s=2e-4, pre=0, seed=11)
+    sig = 0.01 * (rng.standard_normal(40_000) + 1j * rng.standard_normal(40_000))
+    sig[17_003:17_003 + len(body)] += body
+    sig = sig.astype(np.complex64)
+    want = O.detect_packet_bounds(sig, 56e6, ratio)
+    got = vb.detect_packet_bounds(sig, 56e6, ratio)
+    assert tuple(int(v) for v in got) == want
+    got_dev = vb.detect_packet_bounds(torch.from_numpy(sig).to(eng.device), 56e6, ratio)
+    assert tuple(got_dev) == want
+    assert 17_003 - 56 <= want[0] <= 17_003 + 56
+
+
+def test_detect_packet_bounds_smoothing_and_degenerate_cases(eng):
+    import vector_b200 as vb
+    rng = np.random.default_rng(3)
+    sig = (rng.standard_normal(5000) + 1j * rng.standard_normal(5000)).astype(np.complex64)
+    sm, mx = eng.box_energy(torch.from_numpy(sig).to(eng.device), 56)
+    ref = np.convolve(np.abs(sig) ** 2, np.ones(56) / 56, mode="same")
+    assert np.max(np.abs(sm.cpu().numpy() - ref)) <= 1e-6 * ref.max()            # numpy's |complex64| is a 2-ulp float32 hypot
+    assert abs(mx.item() - ref.max()) <= 1e-6 * ref.max()
+    z = np.zeros(1000, np.complex64)
+    assert tuple(vb.detect_packet_bounds(z, 56e6)) == O.detect_packet_bounds(z, 56e6)     # threshold 0: every sample
+    with pytest.raises(ValueError):
+        vb.detect_packet_bounds(np.zeros(10, np.complex64), 56e6)
+
+
+@pytest.mark.parametrize("shape", [(1024, 37), (2048, 5), (1, 9), (7, 1)])
+def test_median_filter_rows2_matches_scipy(eng, shape):
+    import vector_b200 as vb
+    rng = np.random.default_rng(shape[0])
+    a = (rng.standard_normal(shape) * 20 - 60).astype(np.float32)
+    want = O.median_filter_rows2(a)
+    assert np.array_equal(vb.median_filter_rows2(a), want)
+    d = torch.from_numpy(a).to(eng.device)
+    assert np.array_equal(vb.median_filter_rows2(d).cpu().numpy(), want)                 # C-order rows
+    fm = torch.from_numpy(np.ascontiguousarray(a.T)).to(eng.device).t()                  # frame-major memory, same values
+    out = vb.median_filter_rows2(fm)
+    assert out.stride() == fm.stride() and np.array_equal(out.cpu().numpy(), want)

@@ -15,11 +15,13 @@ __all__ = ["resample_signal", "apply_frequency_shift", "create_spectrogram",
            "normalize_spectrogram", "save_vector", "save_vector_wv", "load_packet",
            "load_packet_info", "compute_freq_ranges", "build_vector", "build_vector_device",
            "create_spectrogram_device", "full_rate_spectrogram_device", "install", "Engine",
-           "get_engine", "validate_packet_timing", "TARGET_SAMPLE_RATE", "MAX_PACKETS"]
+           "get_engine", "validate_packet_timing", "TARGET_SAMPLE_RATE", "MAX_PACKETS",
+           "detect_packet_bounds", "median_filter_rows2"]
 
 _API = {"resample_signal", "apply_frequency_shift", "create_spectrogram", "normalize_spectrogram",
         "save_vector", "save_vector_wv", "load_packet", "load_packet_info", "compute_freq_ranges",
-        "create_spectrogram_device", "full_rate_spectrogram_device", "wv_header"}
+        "create_spectrogram_device", "full_rate_spectrogram_device", "wv_header",
+        "detect_packet_bounds", "median_filter_rows2"}
 _GEN = {"build_vector", "build_vector_device", "install"}
 _ENG = {"Engine", "get_engine"}
 

@@ -67,6 +67,10 @@ _SIGNATURES = {
                                        C.POINTER(C.c_int64), C.c_int, C.POINTER(C.c_float),
                                        C.c_void_p]),
     "b200vec_wv_quantize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "b200vec_box_energy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200vec_threshold_bounds": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.POINTER(C.c_int64), C.c_void_p]),
+    "b200vec_median2_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
+                                       C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b200vec_split_planes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 

@@ -276,3 +276,52 @@ def normalize_spectrogram(Sxx, low_percentile=10.0, high_percentile=95.0, max_dy
     if Sxx.dtype == np.float64:
         out, vmin, vmax = out.astype(np.float64), np.float64(vmin), np.float64(vmax)
     return out, vmin, vmax
+
+
+# ------------------------------------------------------------------------------ either side of the path
+def detect_packet_bounds(signal, sample_rate, threshold_ratio=0.2):
+    """Drop-in for utils.detect_packet_bounds (utils.py:811-825): (start, end) sample indices of the
+    packet — |x|^2 box-smoothed over 1 us (np.convolve 'same' in float64), threshold at noise +
+    ratio * (peak - noise) with noise = median of the first tenth, first / last sample above it;
+    (0, len(signal)) when nothing is above.  `signal`: numpy array or complex64 CUDA tensor.
+    Smoothing, peak and the index search run on the device (K8/K9); the median is an exact order
+    statistic of the device array (sorted there), the two scalars are combined on the host in double
+    precision exactly like the reference's numpy scalars."""
+    eng = get_engine(signal.device) if isinstance(signal, torch.Tensor) and signal.is_cuda else get_engine()
+    if isinstance(signal, torch.Tensor):
+        dev = signal.reshape(-1).to(device=eng.device, dtype=torch.complex64)
+    else:
+        dev = torch.from_numpy(np.ascontiguousarray(np.asarray(signal).reshape(-1).astype(np.complex64))).to(eng.device)
+    n = dev.numel()
+    window = max(1, int(sample_rate // 1_000_000))
+    if n == 0 or n < window or window > 1024:
+        raise ValueError("detect_packet_bounds: the signal must be at least one smoothing window "
+                         f"({window} samples, at most 1024) long")
+    smoothed, max_en = eng.box_energy(dev, window)
+    head = smoothed[: max(1, n // 10)]
+    srt, _ = torch.sort(head)
+    m = srt.numel()
+    noise = float(srt[m // 2]) if m % 2 else float((srt[m // 2 - 1] + srt[m // 2]) / 2)     # np.median
+    max_en = float(max_en)
+    threshold = noise + threshold_ratio * (max_en - noise)
+    first, last = eng.threshold_bounds(smoothed, threshold)
+    if last < 0:
+        return 0, n
+    return first, last
+
+
+def median_filter_rows2(Sxx_db, engine=None):
+    """scipy.ndimage.median_filter(Sxx_db, size=(2, 1)) as plot_spectrogram applies it before display
+    (utils.py:435-440): each bin takes the larger of itself and the bin one row up (row 0 unchanged).
+    numpy in -> numpy out; CUDA tensor in -> CUDA tensor out (same layout)."""
+    if isinstance(Sxx_db, torch.Tensor) and Sxx_db.is_cuda:
+        eng = engine or get_engine(Sxx_db.device)
+        return eng.median2_rows(Sxx_db)
+    a = np.asarray(Sxx_db)
+    if a.ndim != 2:
+        raise ValueError("median_filter_rows2 expects a 2-D array")
+    if a.size == 0:
+        return a.copy()
+    eng = engine or get_engine()
+    dev = torch.from_numpy(np.ascontiguousarray(a.astype(np.float32, copy=False))).to(eng.device)
+    return eng.median2_rows(dev).cpu().numpy().astype(a.dtype, copy=False)

@@ -8,6 +8,7 @@
 #include "fused1024.cuh"
 #include "pipe1024.cuh"
 #include "wf1024.cuh"
+#include "packet.cuh"
 #include "select.cuh"
 
 namespace b200vec {
@@ -565,6 +566,62 @@ int b200vec_split_planes(b200vec_ctx *ctx, const void *in_dev, int64_t n, float 
     const long long cap = (long long)ctx->sm_count * 8;
     if (grid > cap) grid = cap;
     split_planes_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>((const float2 *)in_dev, n, re_out_dev, im_out_dev);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int b200vec_box_energy(b200vec_ctx *ctx, const void *in_dev, int64_t n, int window, double *smoothed_out_dev,
+                       double *max_out_dev, void *stream) {
+    B2_REQUIRE(ctx && n >= 0 && (n == 0 || (in_dev && smoothed_out_dev)) && max_out_dev, "NULL argument");
+    B2_REQUIRE(window >= 1 && window <= kBoxMaxWindow, "window must be in [1, 1024]");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    B2_CUDA(cudaMemsetAsync(max_out_dev, 0, sizeof(double), st));
+    if (n == 0) return 0;
+    long long grid = (n + kBoxThreads - 1) / kBoxThreads;
+    const long long cap = (long long)ctx->sm_count * 8;
+    if (grid > cap) grid = cap;
+    box_energy_kernel<<<(unsigned)grid, kBoxThreads, 0, st>>>((const float2 *)in_dev, n, window, smoothed_out_dev,
+                                                              reinterpret_cast<unsigned long long *>(max_out_dev));
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int b200vec_threshold_bounds(b200vec_ctx *ctx, const double *smoothed_dev, int64_t n, double threshold,
+                             int64_t *first_last_host, void *stream) {
+    B2_REQUIRE(ctx && first_last_host && n >= 0 && (n == 0 || smoothed_dev), "NULL argument");
+    first_last_host[0] = n; first_last_host[1] = -1;
+    if (n == 0) return 0;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    long long *dev = reinterpret_cast<long long *>(ctx->hist);          // select scratch doubles as the 2-slot result
+    long long *pin = reinterpret_cast<long long *>(ctx->pinned);
+    pin[0] = n; pin[1] = -1;
+    B2_CUDA(cudaMemcpyAsync(dev, pin, 2 * sizeof(long long), cudaMemcpyHostToDevice, st));
+    long long grid = (n + 255) / 256;
+    const long long cap = (long long)ctx->sm_count * 8;
+    if (grid > cap) grid = cap;
+    threshold_bounds_kernel<<<(unsigned)grid, 256, 0, st>>>(smoothed_dev, n, threshold, dev);
+    B2_CUDA(cudaGetLastError());
+    B2_CUDA(cudaMemcpyAsync(pin, dev, 2 * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    first_last_host[0] = pin[0]; first_last_host[1] = pin[1];
+    return 0;
+}
+
+int b200vec_median2_rows(b200vec_ctx *ctx, const float *in_dev, int64_t rows, int64_t cols, int64_t in_row_stride,
+                         int64_t in_col_stride, float *out_dev, int64_t out_row_stride, int64_t out_col_stride,
+                         void *stream) {
+    B2_REQUIRE(ctx && rows >= 0 && cols >= 0, "bad geometry");
+    if (rows == 0 || cols == 0) return 0;
+    B2_REQUIRE(in_dev && out_dev && in_dev != out_dev, "NULL argument or in-place call");
+    DeviceGuard g(ctx->device);
+    long long grid = (rows * cols + 255) / 256;
+    const long long cap = (long long)ctx->sm_count * 16;
+    if (grid > cap) grid = cap;
+    const int cols_fast = llabs(in_col_stride) <= llabs(in_row_stride);   // walk the contiguous direction with threadIdx
+    median2_rows_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(in_dev, rows, cols, in_row_stride, in_col_stride,
+                                                                          out_dev, out_row_stride, out_col_stride, cols_fast);
     B2_CUDA(cudaGetLastError());
     return 0;
 }

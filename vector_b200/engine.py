@@ -317,6 +317,40 @@ def _split_planes(self, x, out=None):
 Engine.split_planes = _split_planes
 
 
+def _box_energy(self, x, window):
+    """(smoothed float64 [n], max float64 [1]) — b200vec_box_energy (utils.py:813-816)."""
+    x = x.reshape(-1)
+    out = torch.empty(x.numel(), dtype=torch.float64, device=self.device)
+    mx = torch.empty(1, dtype=torch.float64, device=self.device)
+    check(self.lib.b200vec_box_energy(self._ctx, self._ptr(x), x.numel(), int(window), self._ptr(out),
+                                      self._ptr(mx), self._stream()))
+    self.launches += 1
+    return out, mx
+
+
+def _threshold_bounds(self, smoothed, threshold):
+    """(first, last) index with smoothed >= threshold; (n, -1) when none — b200vec_threshold_bounds."""
+    res = (C.c_int64 * 2)()
+    check(self.lib.b200vec_threshold_bounds(self._ctx, self._ptr(smoothed), smoothed.numel(), float(threshold),
+                                            res, self._stream()))
+    self.launches += 1
+    return int(res[0]), int(res[1])
+
+
+def _median2_rows(self, s):
+    """max(s[r-1], s[r]) per column, row 0 kept — b200vec_median2_rows; output has s's layout."""
+    out = torch.empty_strided(s.shape, s.stride(), dtype=torch.float32, device=self.device)
+    check(self.lib.b200vec_median2_rows(self._ctx, self._ptr(s), s.shape[0], s.shape[1], s.stride(0), s.stride(1),
+                                        self._ptr(out), out.stride(0), out.stride(1), self._stream()))
+    self.launches += 1
+    return out
+
+
+Engine.box_energy = _box_energy
+Engine.threshold_bounds = _threshold_bounds
+Engine.median2_rows = _median2_rows
+
+
 def get_engine(device=None):
     """Process-wide Engine for `device` (default: torch's current CUDA device)."""
     if not torch.cuda.is_available():

@@ -217,7 +217,7 @@ def make_main_generate_vector(ns):
 
 _PATCHED_NAMES = ("resample_signal", "apply_frequency_shift", "create_spectrogram",
                   "normalize_spectrogram", "save_vector", "save_vector_wv", "load_packet",
-                  "load_packet_info", "compute_freq_ranges")
+                  "load_packet_info", "compute_freq_ranges", "detect_packet_bounds")
 
 
 def install(utils_mod=None, unified_gui_mod=None, main_mod=None):
