@@ -87,10 +87,33 @@ struct WfArgs {
     unsigned int *ctr;           // [0] next work item, [1] finished CTAs, [2] grid barrier, [4..5] max |v|^2 bits (all zero between launches); [3] epoch published, [6..7] combined max (peer mode)
 };
 
+// Packet-bank loads ask L2 to keep their lines (evict_last) and the output leaves with evict_first, so the
+// ~5 MB bank survives the 896 MB the kernel streams through the 126 MB L2 — between steps too: pass A of
+// the next launch starts on a warm bank.
+__device__ __forceinline__ unsigned long long wf_policy_evict_last() {
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ float2 wf_ldg_keep(const float2 *p, unsigned long long pol) {
+    float2 v;
+    asm volatile("ld.global.nc.L2::cache_hint.v2.f32 {%0, %1}, [%2], %3;" : "=f"(v.x), "=f"(v.y) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ unsigned long long wf_policy_evict_first() {
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void wf_bulk_s2g(void *dst, unsigned src, unsigned bytes, unsigned long long pol) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
+                 ::"l"(dst), "r"(src), "r"(bytes), "l"(pol) : "memory");
+}
+
 // B: the 512 samples starting `off` samples into the item's span.  Returns false when no packet
 // instance overlaps them (x is then exactly zero).
 __device__ __forceinline__ bool wf_build_half(const WfArgs &a, unsigned active, int cnt_l, int rel0_l, int off,
-                                              int lane, float2 (&x)[16]) {
+                                              int lane, float2 (&x)[16], unsigned long long keep) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) x[j] = make_float2(0.f, 0.f);
     bool live = false;
@@ -111,7 +134,7 @@ __device__ __forceinline__ bool wf_build_half(const WfArgs &a, unsigned active, 
             if (r >= 0 && r + 512 <= len) {
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
-                    const float2 v = __ldg(base + 32 * j);
+                    const float2 v = wf_ldg_keep(base + 32 * j, keep);
                     x[j].x += v.x; x[j].y += v.y;
                 }
             } else {
@@ -119,7 +142,7 @@ __device__ __forceinline__ bool wf_build_half(const WfArgs &a, unsigned active, 
                 for (int j = 0; j < 16; ++j) {
                     const int n = r + lane + 32 * j;
                     if (n >= 0 && n < len) {
-                        const float2 v = __ldg(base + 32 * j);
+                        const float2 v = wf_ldg_keep(base + 32 * j, keep);
                         x[j].x += v.x; x[j].y += v.y;
                     }
                 }
@@ -141,7 +164,8 @@ __device__ __forceinline__ void wf_fence_async() { asm volatile("fence.proxy.asy
 // 32-point transform old by then, so the wait is normally free.
 template <bool STORE, bool BULK>
 __device__ __forceinline__ void wf_store_half(float2 *vec, long long s, long long n_vec, bool live, float scl,
-                                              int lane, float2 (&x)[16], float2 *vst, unsigned zero_u32) {
+                                              int lane, float2 (&x)[16], float2 *vst, unsigned zero_u32,
+                                              unsigned long long pol) {
     if (live) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) { x[j].x *= scl; x[j].y *= scl; }
@@ -157,9 +181,9 @@ __device__ __forceinline__ void wf_store_half(float2 *vec, long long s, long lon
                 for (int j = 0; j < 16; ++j) vst[lane + 32 * j] = x[j];
                 wf_fence_async();
                 __syncwarp();
-                if (lane == 0) { tma_bulk_s2g(dst, smem_u32(vst), 4096u); tma_store_commit(); }
+                if (lane == 0) { wf_bulk_s2g(dst, smem_u32(vst), 4096u, pol); tma_store_commit(); }
             } else if (lane == 0) {
-                tma_bulk_s2g(dst, zero_u32, 4096u); tma_store_commit();
+                wf_bulk_s2g(dst, zero_u32, 4096u, pol); tma_store_commit();
             }
         } else if (live) {
 #pragma unroll
@@ -212,6 +236,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
             wf[i] = __ldg(a.window + ln + 32 * brev5(4 * k + c)) * rs;
         }
     }
+    const unsigned long long keep = wf_policy_evict_last();
     float scl = 1.0f;
     if (a.mode == B200VEC_BUILD_SCALE) {
         const double m2 = __longlong_as_double((long long)*a.maxsq);
@@ -250,7 +275,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                 const int valid = (int)(s1 - s0) - 512 * half;
                 if (valid <= 0) break;
                 float2 x[16];
-                if (!wf_build_half(a, active, cnt_l, rel0_l, 512 * half, lane, x)) continue;
+                if (!wf_build_half(a, active, cnt_l, rel0_l, 512 * half, lane, x, keep)) continue;
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                     const float q = (lane + 32 * j < valid) ? x[j].x * x[j].x + x[j].y * x[j].y : 0.f;
@@ -317,6 +342,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
     const float2 *ex_r = exch + lane;                        // T2 reads column q = lane
     unsigned anybits = 0;
     const bool track = a.flag != nullptr;
+    const unsigned long long pol = wf_policy_evict_first();
 
     unsigned next = 0;
     if (lane == 0) next = atomicAdd(a.ctr, 1u);
@@ -349,8 +375,8 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) xo[j] = __ldcs(src + 32 * j);
         } else {
-            live_o = wf_build_half(a, active, cnt_l, rel0_l, 0, lane, xo);
-            wf_store_half<!(DBG & 2), BULK>(a.vec, h0 * 512, n_vec, live_o, scl, lane, xo, vst, zero_u32);
+            live_o = wf_build_half(a, active, cnt_l, rel0_l, 0, lane, xo, keep);
+            wf_store_half<!(DBG & 2), BULK>(a.vec, h0 * 512, n_vec, live_o, scl, lane, xo, vst, zero_u32, pol);
         }
 #pragma unroll 1
         for (int i = 0; i < cn; ++i) {
@@ -364,8 +390,8 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
 #pragma unroll
                 for (int j = 0; j < 16; ++j) xn[j] = __ldcs(src + 32 * j);
             } else {
-                live_n = wf_build_half(a, active, cnt_l, rel0_l, (i + 1) * 512, lane, xn);
-                wf_store_half<!(DBG & 2), BULK>(a.vec, sv ? (h + 1) * 512 : n_vec, n_vec, live_n, scl, lane, xn, vst, zero_u32);
+                live_n = wf_build_half(a, active, cnt_l, rel0_l, (i + 1) * 512, lane, xn, keep);
+                wf_store_half<!(DBG & 2), BULK>(a.vec, sv ? (h + 1) * 512 : n_vec, n_vec, live_n, scl, lane, xn, vst, zero_u32, pol);
             }
             if (fv) {
                 float *of = a.out + h * a.out_ld;
@@ -407,10 +433,10 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                     if (BULK) {
                         wf_fence_async();
                         __syncwarp();
-                        if (lane == 0 && !(DBG & 1)) { tma_bulk_s2g(of, smem_u32(exch), 4096u); tma_store_commit(); }
+                        if (lane == 0 && !(DBG & 1)) { wf_bulk_s2g(of, smem_u32(exch), 4096u, pol); tma_store_commit(); }
                     }
                 } else if (BULK) {
-                    if (lane == 0 && !(DBG & 1)) { tma_bulk_s2g(of, zero_u32, 4096u); tma_store_commit(); }
+                    if (lane == 0 && !(DBG & 1)) { wf_bulk_s2g(of, zero_u32, 4096u, pol); tma_store_commit(); }
                 } else {
                     float4 *o4 = reinterpret_cast<float4 *>(of) + lane;
 #pragma unroll
