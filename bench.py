@@ -167,7 +167,7 @@ def run_ours(args):
     n_frames = plan.frame_hi - plan.frame_lo
     vec = torch.empty(n_own, dtype=torch.complex64, device=eng.device)
     spec = eng.alloc_spectrogram(1024, n_frames, frame_major=not args.rows)   # [1024, frames] view of [frames, 1024] memory
-    descs, nd = eng.make_descs(rows)
+    descs, nd = eng.make_descs(rows, eng.free_flags(rows, total))   # hint bit for the in-kernel max pass
     max_ranges = eng.max_ranges(rows, total, world, rank)      # this rank's share of one common period + head/tail
     from vector_b200._lib import BUILD_MAXONLY, BUILD_SCALE
 

@@ -16,7 +16,8 @@ plan = vdist.plan_slab(N, 1, 0, 1024, 512, 1, align=512)
 nf = plan.frame_hi - plan.frame_lo
 vec = torch.empty(N, dtype=torch.complex64, device=eng.device)
 spec = eng.alloc_spectrogram(1024, nf, frame_major=True)
-descs, nd = eng.make_descs(rows)
+descs, nd = eng.make_descs(rows, eng.free_flags(rows, N) if os.environ.get('NOFLAGS') != '1' else None)
+print('free-instance flags:', eng.free_flags(rows, N))
 ranges = eng.max_ranges(rows, N)
 eng._maxsq.zero_(); eng.max_pass(descs, nd, ranges)
 keep = eng._maxsq.clone()

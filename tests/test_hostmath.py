@@ -270,3 +270,35 @@ def test_save_vector_flattens_and_casts(tmp_path):
     api.save_vector(v, str(tmp_path / "m.mat"))
     back = sio.loadmat(str(tmp_path / "m.mat"))["Y"]
     assert back.shape == (1, 12) and back.dtype == np.complex64 and np.array_equal(back.ravel(), v.ravel().astype(np.complex64))
+
+
+# ------------------------------------------------------------------------------ free-instance hint
+def _brute_free_flags(rows, lengths, total):
+    inst = [(s + k * p, s + k * p + n, i) for i, ((s, p, c, _), n) in enumerate(zip(rows, lengths)) for k in range(c)]
+    flags = [False] * len(rows)
+    for a0, a1, i in inst:
+        if a1 > total:
+            continue
+        if all(not (b0 < a1 and b1 > a0) for b0, b1, j in inst if (b0, b1, j) != (a0, a1, i)) and \
+           sum(1 for x in inst if x == (a0, a1, i)) == 1:
+            flags[i] = True
+    return flags
+
+
+def test_free_instance_flags_match_brute_force():
+    rng = np.random.default_rng(42)
+    for _ in range(200):
+        npk = int(rng.integers(1, 5))
+        total = int(rng.integers(200, 3000))
+        rows, lengths = [], []
+        for i in range(npk):
+            n = int(rng.integers(5, 200))
+            period = int(rng.integers(max(1, n // 2), 4 * n))       # sometimes shorter than the packet: self-overlap
+            start = int(rng.integers(0, 300))
+            rows.append((start, period, H.instance_count(start, period, n, total), i))
+            lengths.append(n)
+        assert H.free_instance_flags(rows, lengths, total) == _brute_free_flags(rows, lengths, total)
+    assert H.free_instance_flags([(0, 10, 0, 0)], [5], 100) == [False]
+    assert H.free_instance_flags([(0, 10, 3, 0)], [5], 100) == [True]
+    assert H.free_instance_flags([(0, 4, 3, 0)], [5], 100) == [False]                     # every instance overlaps a neighbour
+    assert H.free_instance_flags([(0, 10, 3, 0)], [5], 100, max_instances=2) == [False]   # conservative cap

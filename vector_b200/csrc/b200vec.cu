@@ -133,6 +133,7 @@ int b200vec_destroy(b200vec_ctx *ctx) {
     if (ctx->hist) cudaFree(ctx->hist);
     if (ctx->zeros) cudaFree(ctx->zeros);
     if (ctx->wf_ctr) cudaFree(ctx->wf_ctr);
+    if (ctx->slot_max) cudaFree(ctx->slot_max);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     delete ctx;
     return 0;
@@ -200,6 +201,10 @@ int b200vec_bank_shift(b200vec_ctx *ctx, int slot, double freq_hz, double fs_hz,
     shift_commit_kernel<<<(unsigned)((len + 255) / 256), 256, 0, st>>>(
         sl.raw, len, w, fs_hz, freq_hz != 0.0 ? 1 : 0, sl.a, sl.b);
     B2_CUDA(cudaGetLastError());
+    if (!ctx->slot_max) B2_CUDA(cudaMalloc(&ctx->slot_max, sizeof(unsigned long long) * B200VEC_MAX_SLOTS));
+    B2_CUDA(cudaMemsetAsync(ctx->slot_max + slot, 0, sizeof(unsigned long long), st));
+    bank_maxsq_kernel<<<(unsigned)((len + 1023) / 1024 < 64 ? (len + 1023) / 1024 : 64), 256, 0, st>>>(sl.a, len, ctx->slot_max + slot);
+    B2_CUDA(cudaGetLastError());
     sl.len = len;
     return 0;
 }
@@ -250,6 +255,7 @@ int b200vec_build(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
         PlaceDesc &p = args.d[np++];
         p.start = d.start; p.period = d.period; p.count = d.count;
         p.len = (int)sl.len; p.a = sl.a; p.b = sl.b;
+        p.free_inst = d.reserved & 1; p.pmax = ctx->slot_max + d.slot;
     }
     args.np = np;
     DeviceGuard g(ctx->device);
@@ -313,6 +319,7 @@ static int fill_place_args(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
         PlaceDesc &p = args.d[np++];
         p.start = d.start; p.period = d.period; p.count = d.count;
         p.len = (int)sl.len; p.a = sl.a; p.b = sl.b;
+        p.free_inst = d.reserved & 1; p.pmax = ctx->slot_max + d.slot;
     }
     args.np = np;
     return 0;

@@ -31,6 +31,19 @@ shift_commit_kernel(const float2 *__restrict__ raw, long long len, double w, dou
     b[n] = y;
 }
 
+// max |y|^2 (exact float32 products, in fp64) over a committed packet -> *out (bits, atomicMax; zeroed by the caller)
+__global__ void __launch_bounds__(256)
+bank_maxsq_kernel(const float2 *__restrict__ y, long long len, unsigned long long *__restrict__ out) {
+    double m = 0.0;
+    for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < len; n += (long long)gridDim.x * blockDim.x) {
+        const float2 v = y[n];
+        m = fmax(m, (double)v.x * (double)v.x + (double)v.y * (double)v.y);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0.0) atomicMax(out, (unsigned long long)__double_as_longlong(m));
+}
+
 // ---------------------------------------------------------------------------------------
 // K0: scipy.signal.resample(x, num) for complex input (reference call site utils.py:117),
 // i.e. X = fft(x); Y = zeros(num); copy the m = min(num, n_x) lowest-|f| bins; if m is even

@@ -68,5 +68,6 @@ struct b200vec_ctx {
     void *pinned = nullptr;               // small pinned staging block
     float2 *zeros = nullptr;              // one span of zero samples (bulk-copy source, fused1024.cuh)
     unsigned int *wf_ctr = nullptr;       // work-item counter of the warp-per-frame kernel (wf1024.cuh)
+    unsigned long long *slot_max = nullptr;   // per bank slot: bits of max |y|^2 (double) of the committed packet
     int sm_count = b200vec::kSmCount;
 };

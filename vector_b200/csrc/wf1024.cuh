@@ -110,6 +110,30 @@ __device__ __forceinline__ void wf_bulk_s2g(void *dst, unsigned src, unsigned by
                  ::"l"(dst), "r"(src), "r"(bytes), "l"(pol) : "memory");
 }
 
+// Pass A only: true when the 512 samples at `off` lie inside exactly ONE instance, of a packet whose
+// whole-packet max is known to be attained elsewhere in the vector (PlaceDesc::free_inst) — their
+// |v|^2 cannot exceed that max (it enters the reduction through PlaceDesc::pmax), so nothing is read.
+__device__ __forceinline__ bool wf_norm_can_skip(const WfArgs &a, unsigned active, int cnt_l, int rel0_l, int off) {
+    int n_ov = 0;
+    bool ok = false;
+    for (unsigned m = active; m; m &= m - 1) {
+        const int p = __ffs(m) - 1;
+        const int cnt = __shfl_sync(0xffffffffu, cnt_l, p);
+        const int rel0 = __shfl_sync(0xffffffffu, rel0_l, p);
+        const PlaceDesc &d = a.place.d[p];
+        const int len = d.len;
+        const long long period = d.period;
+        long long r64 = (long long)rel0 + off;
+        for (int i = 0; i < cnt; ++i, r64 -= period) {
+            if (r64 + 512 <= 0) break;
+            if (r64 >= len) continue;
+            ++n_ov;
+            ok = d.free_inst && r64 >= 0 && r64 + 512 <= len;
+        }
+    }
+    return n_ov == 1 && ok;
+}
+
 // B: the 512 samples starting `off` samples into the item's span.  Returns false when no packet
 // instance overlaps them (x is then exactly zero).
 __device__ __forceinline__ bool wf_build_half(const WfArgs &a, unsigned active, int cnt_l, int rel0_l, int off,
@@ -275,6 +299,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                 const int valid = (int)(s1 - s0) - 512 * half;
                 if (valid <= 0) break;
                 float2 x[16];
+                if (wf_norm_can_skip(a, active, cnt_l, rel0_l, 512 * half)) continue;
                 if (!wf_build_half(a, active, cnt_l, rel0_l, 512 * half, lane, x, keep)) continue;
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
@@ -288,6 +313,10 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         }
         tmax = warp_max(tmax);
         if (lane == 0 && tmax > 0.0) atomicMax(slot, (unsigned long long)__double_as_longlong(tmax));
+        if (blockIdx.x == 0 && warp == 0 && lane < a.place.np && a.place.d[lane].free_inst) {
+            const unsigned long long pm = *a.place.d[lane].pmax;          // max |y|^2 over the whole packet
+            if (pm) atomicMax(slot, pm);
+        }
         __syncthreads();
         if (tid == 0) {                                      // grid barrier
             __threadfence();

@@ -130,9 +130,10 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
         out_vec = torch.empty(max(n, 0), dtype=torch.complex64, device=engine.device)
     if out_spec is None:
         out_spec = engine.alloc_spectrogram(1024, nf, frame_major=True)
-    descs, nd = engine.make_descs(rows)
-    mode, norm_ranges = BUILD_STORE, None
     frame_major = out_spec.dim() == 2 and out_spec.stride(0) == 1 and out_spec.stride(1) >= 1024
+    in_kernel_max = normalize and frame_major and (peer is not None or (plan.world == 1 and reduce_max is None))
+    descs, nd = engine.make_descs(rows, engine.free_flags(rows, plan.total) if in_kernel_max else None)
+    mode, norm_ranges = BUILD_STORE, None
     if normalize and peer is not None and frame_major:
         # multi-GPU, ONE launch per rank: this rank's share of pass A and the MAX exchange over NVLink
         # peer memory both run inside the fused kernel (no NCCL call in the step)

@@ -85,13 +85,28 @@ class Engine:
 
     # ------------------------------------------------------------------ vector build
     @staticmethod
-    def make_descs(rows):
-        """rows: iterable of (start, period, count, slot) -> ctypes array of b200vec_pkt_desc."""
+    def make_descs(rows, free_flags=None):
+        """rows: iterable of (start, period, count, slot) -> ctypes array of b200vec_pkt_desc.
+        free_flags (hostmath.free_instance_flags): sets bit 0 of `reserved`, the hint that lets the
+        in-kernel max pass skip spans inside a single instance."""
         rows = list(rows)
         arr = (PktDesc * max(1, len(rows)))()
         for i, (start, period, count, slot) in enumerate(rows):
-            arr[i] = PktDesc(int(start), int(period), int(count), int(slot), 0)
+            arr[i] = PktDesc(int(start), int(period), int(count), int(slot),
+                             1 if (free_flags is not None and free_flags[i]) else 0)
         return arr, len(rows)
+
+    def free_flags(self, rows, total):
+        """hostmath.free_instance_flags for these rows, cached (the interval sweep is host work that
+        would otherwise be repeated for every step of an unchanged scenario)."""
+        rows = [tuple(int(v) for v in r) for r in rows]
+        key = (tuple(rows), tuple(self.bank_len(r[3]) for r in rows), int(total))
+        cache = self.__dict__.setdefault("_free_flag_cache", {})
+        if key not in cache:
+            if len(cache) > 64:
+                cache.clear()
+            cache[key] = H.free_instance_flags(rows, list(key[1]), total)
+        return cache[key]
 
     def build_pass(self, descs, n_descs, lo, hi, out, mode, maxsq=None):
         maxsq = self._maxsq if maxsq is None else maxsq

@@ -461,3 +461,28 @@ def split_ranges(ranges, world, rank):
             out.append((lo + x0 - pos, lo + x1 - pos))
         pos += n
     return out
+
+
+def free_instance_flags(rows, lengths, total, max_instances=4_000_000):
+    """Per packet: does at least one of its instances lie in [0, total) with NO other instance (of any
+    packet, itself included) over any of its samples?  Then every sample of the packet appears
+    unsummed somewhere in the vector, so max|y_p|^2 over the whole packet is attained by the vector
+    and the in-kernel max pass may skip spans lying inside exactly one instance of it
+    (b200vec_pkt_desc.reserved bit 0).  rows: (start, period, count, slot).  Conservative: all False
+    when there are more than `max_instances` instances."""
+    rows = [(int(s), int(p), int(k)) for s, p, k, _ in rows]
+    n_inst = sum(k for _, _, k in rows)
+    flags = [False] * len(rows)
+    if n_inst == 0 or n_inst > max_instances:
+        return flags
+    starts = np.concatenate([s + p * np.arange(k, dtype=np.int64) for s, p, k in rows])
+    ends = starts + np.concatenate([np.full(k, int(n), np.int64) for (_, _, k), n in zip(rows, lengths)])
+    owner = np.concatenate([np.full(k, i, np.int64) for i, (_, _, k) in enumerate(rows)])
+    order = np.argsort(starts, kind="stable")
+    st, en, ow = starts[order], ends[order], owner[order]
+    prev_end = np.concatenate([[np.iinfo(np.int64).min], np.maximum.accumulate(en)[:-1]])
+    next_start = np.concatenate([np.minimum.accumulate(st[::-1])[::-1][1:], [np.iinfo(np.int64).max]])
+    free = (prev_end <= st) & (next_start >= en) & (en <= int(total))
+    for i in np.unique(ow[free]):
+        flags[int(i)] = True
+    return flags
