@@ -14,13 +14,22 @@
 // [frames, 1024] (the array handed to Python is its transpose VIEW: same shape, dtype and values as
 // the reference's, Fortran-ordered).  One frame's 1024 bins are then 4 KB of contiguous memory, a
 // whole 1024-point transform fits inside ONE warp, and nothing is shared between warps:
-//   * no block barrier in the main loop (two __syncwarp per frame), no TMA, no mbarrier;
+//   * no block barrier in the main loop (a few __syncwarp per frame), no mbarrier;
 //   * 16 independent warps per SM drift out of phase, so one warp's L2 gather, another's
 //     shared-memory exchange, another's FMAs and another's stores overlap;
-//   * every spectrogram store instruction writes one full 128-byte line at an immediate offset.
+//   * a frame's 4 KB of PSD and a half's 4 KB of samples each leave as ONE bulk copy
+//     (cp.async.bulk shared -> global, L2 evict_first) out of the warp's own staging blocks, so the
+//     stores occupy neither registers nor the LSU queue the exchange needs (direct 128-byte-line
+//     stores remain as the B200VEC_WF_BULK=0 A/B path); bank loads carry an L2 evict_last hint.
+// Normalisation: the caller supplies the max (SCALE), or the kernel finds it first (kWfAutoNorm:
+// every warp reduces its share of the max ranges, grid barrier under a cooperative launch), or —
+// multi-GPU — additionally MAX-combines it with the other GPUs through NVLink peer memory
+// (kWfAutoNormPeer): the path's only collective, inside the one launch.
+// PLAIN instantiation: stand-alone STFT of an existing vector in the same layout.
 //
 // Work item = kWfChunk consecutive frames, handed out by a global atomic counter (dynamic: live
-// and empty stretches of the vector cost very different amounts).  Per item a warp
+// and empty stretches of the vector cost very different amounts), single frames for the last
+// two items' worth per warp so that the warps run dry together.  Per item a warp
 //   S   finds, per packet (lane p), the instance range overlapping the item's span
 //       (two 64-bit floor divisions), once;
 //   B   builds the next 512 samples: lane l owns x[l + 32 j]; for every overlapping
