@@ -66,12 +66,12 @@ static int run_select(b200vec_ctx *ctx, const float *data, long long n, int posi
     sel_init<<<1, 1, 0, st>>>(ctx->hist, init);
     const unsigned grid = (unsigned)(ctx->sm_count * 8);
     if (n > 0) sel_hist1<<<grid, kSelThreads, 0, st>>>(data, n, positive_only, ctx->hist);
-    sel_pick<1><<<1, 1, 0, st>>>(ctx->hist);
+    sel_pick<1><<<1, kPickThreads, 0, st>>>(ctx->hist);
     if (nr > 0 && n > 0) {
         sel_histN<2><<<grid, kSelThreads, (size_t)nr * kBins2 * 4, st>>>(data, n, positive_only, ctx->hist);
-        sel_pick<2><<<1, 1, 0, st>>>(ctx->hist);
+        sel_pick<2><<<1, kPickThreads, 0, st>>>(ctx->hist);
         sel_histN<3><<<grid, kSelThreads, (size_t)nr * kBins3 * 4, st>>>(data, n, positive_only, ctx->hist);
-        sel_pick<3><<<1, 1, 0, st>>>(ctx->hist);
+        sel_pick<3><<<1, kPickThreads, 0, st>>>(ctx->hist);
     }
     B2_CUDA(cudaGetLastError());
     B2_CUDA(cudaMemcpyAsync(ctx->pinned, ctx->hist + kStateOff, sizeof(SelState),

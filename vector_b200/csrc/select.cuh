@@ -5,8 +5,8 @@
 // np.percentile needs the exact values at one or two integer ranks of the sorted data.
 // Instead of sorting 10^7..10^8 floats, a 3-level MSD radix select runs on order-preserving
 // uint32 keys: 11 + 11 + 10 bits, one streaming pass per level, histograms in shared
-// memory with warp-aggregated atomics (spectrograms are heavy with repeated values — 42 %
-// exact zeros at BASELINE cfg2 — which would serialise naive atomics).
+// memory, the lanes sharing the warp's first bin aggregated into one atomic (spectrograms are heavy
+// with repeated values — 42 % exact zeros at BASELINE cfg2 — which would serialise naive atomics).
 #pragma once
 #include "common.cuh"
 
@@ -42,12 +42,17 @@ __host__ __device__ __forceinline__ float key2f(unsigned int k) {
 #endif
 }
 
-// add 1 to h[bin] for every active lane with pred, one shared atomic per distinct bin per warp
+// add 1 to h[bin] for every lane with pred (all 32 lanes call this together).  The lanes that share the
+// first active lane's bin are counted by one atomic — whole warps of equal values (the exact zeros of empty
+// frames, the floor value of the dB image) cost one shared atomic — the others add themselves.
 __device__ __forceinline__ void warp_hist_add(unsigned int *h, unsigned int bin, bool pred) {
     const unsigned int active = __ballot_sync(0xffffffffu, pred);
-    if (!pred) return;
-    const unsigned int peers = __match_any_sync(active, bin);
-    if ((int)(__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&h[bin], __popc(peers));
+    if (active == 0) return;
+    const int leader = __ffs(active) - 1;
+    const unsigned int b0 = __shfl_sync(0xffffffffu, bin, leader);
+    const unsigned int same = __ballot_sync(0xffffffffu, pred && bin == b0);
+    if ((int)(threadIdx.x & 31) == leader) atomicAdd(&h[b0], __popc(same));
+    else if (pred && bin != b0) atomicAdd(&h[bin], 1u);
 }
 
 __global__ void __launch_bounds__(kSelThreads)
@@ -57,55 +62,106 @@ db_kernel(const float *__restrict__ s, long long n, float floor_val, float *__re
         out[i] = 10.0f * log10f(fabsf(__ldg(s + i)) + floor_val);
 }
 
+// four consecutive elements starting at 4 * g (zeros past n); one 16-byte load when x is 16-byte aligned
+__device__ __forceinline__ void sel_load4(const float *__restrict__ x, long long n, long long g, bool aligned,
+                                          float (&v)[4], bool (&in)[4]) {
+    const long long i = 4 * g;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { v[k] = 0.f; in[k] = i + k < n; }
+    if (aligned && i + 3 < n) {
+        const float4 t = __ldg(reinterpret_cast<const float4 *>(x) + g);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (in[k]) v[k] = __ldg(x + i + k);
+    }
+}
+
+constexpr int kSelUnroll = 4;      // 16-byte loads in flight per thread
+
 // level 1: histogram of the top 11 key bits over all selected elements
 __global__ void __launch_bounds__(kSelThreads)
 sel_hist1(const float *__restrict__ x, long long n, int positive_only, unsigned int *__restrict__ hist) {
     __shared__ unsigned int h[kBins1];
     for (int i = threadIdx.x; i < kBins1; i += kSelThreads) h[i] = 0;
     __syncthreads();
+    const bool aligned = (reinterpret_cast<unsigned long long>(x) & 15ull) == 0;
+    const long long groups = (n + 3) / 4;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long n_round = ((n + stride - 1) / stride) * stride;     // keep warps converged for the ballots
-    for (long long i = i0; i < n_round; i += stride) {
-        float v = 0.f; bool ok = false;
-        if (i < n) { v = __ldg(x + i); ok = positive_only ? (v > 0.f) : true; }
-        warp_hist_add(h, f2key(v) >> 21, ok);
+    const long long g0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long step = stride * kSelUnroll;
+    const long long g_round = ((groups + step - 1) / step) * step;           // keep warps converged for the ballots
+    for (long long g = g0; g < g_round; g += step) {
+        float v[kSelUnroll][4]; bool in[kSelUnroll][4];
+#pragma unroll
+        for (int u = 0; u < kSelUnroll; ++u) sel_load4(x, n, g + u * stride, aligned, v[u], in[u]);
+#pragma unroll
+        for (int u = 0; u < kSelUnroll; ++u)
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                warp_hist_add(h, f2key(v[u][k]) >> 21, in[u][k] && (positive_only ? v[u][k] > 0.f : true));
     }
     __syncthreads();
     for (int i = threadIdx.x; i < kBins1; i += kSelThreads)
         if (h[i]) atomicAdd(&hist[kHist1Off + i], h[i]);
 }
 
-// levels 2 and 3: histogram of the next bits for the elements matching each rank's prefix
+// levels 2 and 3: histogram of the next bits for the elements matching each rank's prefix.
+// A 2048-entry table over the top 11 key bits says which ranks an element can belong to, so the
+// common case (none) costs one shared load per element.
 template <int LEVEL>
 __global__ void __launch_bounds__(kSelThreads)
 sel_histN(const float *__restrict__ x, long long n, int positive_only, unsigned int *__restrict__ hist) {
     constexpr int BINS = (LEVEL == 2) ? kBins2 : kBins3;
     constexpr int SHIFT_PREFIX = (LEVEL == 2) ? 21 : 10;
     extern __shared__ unsigned int hs[];          // [n_ranks][BINS]
+    __shared__ unsigned char lut[2048];
+    __shared__ unsigned int spref[B200VEC_MAX_RANKS];
     const SelState *st = reinterpret_cast<const SelState *>(hist + kStateOff);
     const int nr = st->n_ranks;
     unsigned int pref[B200VEC_MAX_RANKS];
+    unsigned int first = 0;                       // ranks whose prefix no earlier rank has: they own a histogram
 #pragma unroll
-    for (int r = 0; r < B200VEC_MAX_RANKS; ++r) pref[r] = (r < nr) ? st->prefix[r] : 0xffffffffu;
+    for (int r = 0; r < B200VEC_MAX_RANKS; ++r) {
+        pref[r] = (r < nr) ? st->prefix[r] : 0xffffffffu;
+        bool dup = r >= nr;
+        for (int q = 0; q < r; ++q) dup |= (pref[q] == pref[r]);
+        if (!dup) first |= 1u << r;
+    }
+    static_assert(B200VEC_MAX_RANKS <= 8, "one table byte holds one bit per rank");
     for (int i = threadIdx.x; i < nr * BINS; i += kSelThreads) hs[i] = 0;
+    for (int i = threadIdx.x; i < 2048; i += kSelThreads) lut[i] = 0;
     __syncthreads();
+    if (threadIdx.x == 0)
+        for (int r = 0; r < B200VEC_MAX_RANKS; ++r) spref[r] = pref[r];
+    if (threadIdx.x == 0)
+        for (int r = 0; r < B200VEC_MAX_RANKS; ++r)
+            if ((first >> r) & 1u) lut[(LEVEL == 2) ? pref[r] : (pref[r] >> 11)] |= (unsigned char)(1u << r);
+    __syncthreads();
+    const bool aligned = (reinterpret_cast<unsigned long long>(x) & 15ull) == 0;
+    const long long groups = (n + 3) / 4;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long n_round = ((n + stride - 1) / stride) * stride;
-    for (long long i = i0; i < n_round; i += stride) {
-        float v = 0.f; bool ok = false;
-        if (i < n) { v = __ldg(x + i); ok = positive_only ? (v > 0.f) : true; }
-        const unsigned int key = f2key(v);
-        const unsigned int top = key >> SHIFT_PREFIX;
-        const unsigned int bin = (LEVEL == 2) ? ((key >> 10) & 0x7ffu) : (key & 0x3ffu);
+    const long long g0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long step = stride * kSelUnroll;
+    const long long g_round = ((groups + step - 1) / step) * step;
+    for (long long g = g0; g < g_round; g += step) {
+        float v[kSelUnroll][4]; bool in[kSelUnroll][4];
 #pragma unroll
-        for (int r = 0; r < B200VEC_MAX_RANKS; ++r) {
-            if (r < nr) {
-                // identical prefixes share one histogram (the first rank that has it)
-                bool dup = false;
-                for (int q = 0; q < r; ++q) dup |= (pref[q] == pref[r]);
-                if (!dup) warp_hist_add(hs + r * BINS, bin, ok && top == pref[r]);
+        for (int u = 0; u < kSelUnroll; ++u) sel_load4(x, n, g + u * stride, aligned, v[u], in[u]);
+#pragma unroll
+        for (int u = 0; u < kSelUnroll; ++u) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const bool ok = in[u][k] && (positive_only ? v[u][k] > 0.f : true);
+                const unsigned int key = f2key(v[u][k]);
+                unsigned int mine = ok ? lut[key >> 21] : 0u;        // candidate histograms of this element
+                if (!__any_sync(0xffffffffu, mine != 0)) continue;   // most elements match no prefix
+                const unsigned int top = key >> SHIFT_PREFIX;
+                const unsigned int bin = (LEVEL == 2) ? ((key >> 10) & 0x7ffu) : (key & 0x3ffu);
+                for (unsigned int f = first; f; f &= f - 1) {        // warp-uniform: the ranks owning a histogram
+                    const int r = __ffs(f) - 1;
+                    warp_hist_add(hs + r * BINS, bin, ((mine >> r) & 1u) && top == spref[r]);
+                }
             }
         }
     }
@@ -115,21 +171,27 @@ sel_histN(const float *__restrict__ x, long long n, int positive_only, unsigned 
         if (hs[i]) atomicAdd(&hist[off + i], hs[i]);
 }
 
-// single block: walk the level histogram of each rank, refine prefix/resid
+// one block of kPickThreads: block-wide prefix sum over the level histogram of each rank, then the
+// bin holding the rank refines prefix/resid (first bin b with cum(b) + h[b] > want; the last bin if none)
+constexpr int kPickThreads = 1024;
 template <int LEVEL>
-__global__ void __launch_bounds__(1)
+__global__ void __launch_bounds__(kPickThreads)
 sel_pick(unsigned int *__restrict__ hist) {
     SelState *st = reinterpret_cast<SelState *>(hist + kStateOff);
     constexpr int BINS = (LEVEL == 1) ? kBins1 : (LEVEL == 2 ? kBins2 : kBins3);
     constexpr int BITS = (LEVEL == 3) ? 10 : 11;
-    if (LEVEL == 1) {
-        unsigned long long c = 0;
-        for (int b = 0; b < BINS; ++b) c += hist[kHist1Off + b];
-        st->count = c;
-    }
-    unsigned int old[B200VEC_MAX_RANKS];
-    for (int r = 0; r < B200VEC_MAX_RANKS; ++r) old[r] = st->prefix[r];
-    for (int r = 0; r < st->n_ranks; ++r) {
+    constexpr int PER = BINS / kPickThreads;
+    static_assert(PER >= 1 && PER * kPickThreads == BINS, "bins per thread");
+    __shared__ unsigned long long wsum[32];
+    __shared__ unsigned int old[B200VEC_MAX_RANKS];
+    __shared__ int sel_b;
+    __shared__ unsigned long long sel_cum;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int nr = st->n_ranks;
+    if (t < B200VEC_MAX_RANKS) old[t] = st->prefix[t];
+    __syncthreads();
+    const int loops = (LEVEL == 1 && nr == 0) ? 1 : nr;     // level 1 also counts the selected elements
+    for (int r = 0; r < loops; ++r) {
         int src = r;                       // ranks with an identical prefix share the first one's histogram
         if (LEVEL != 1)
             for (int q = r - 1; q >= 0; --q)
@@ -137,16 +199,50 @@ sel_pick(unsigned int *__restrict__ hist) {
         const unsigned int *h = (LEVEL == 1) ? hist + kHist1Off
                               : (LEVEL == 2) ? hist + kHist2Off + src * kBins2
                                              : hist + kHist3Off + src * kBins3;
-        unsigned long long want = st->resid[r], cum = 0;
-        int b = 0;
-        for (; b < BINS - 1; ++b) {
-            const unsigned long long c = h[b];
-            if (cum + c > want) break;
-            cum += c;
+        unsigned int c[PER];
+        unsigned long long s = 0;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) { c[k] = h[t * PER + k]; s += c[k]; }
+        unsigned long long inc = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += up;
         }
-        st->resid[r] = want - cum;
-        st->prefix[r] = (LEVEL == 1) ? (unsigned)b : ((st->prefix[r] << BITS) | (unsigned)b);
-        if (LEVEL == 3) st->result[r] = st->prefix[r];
+        if (lane == 31) wsum[w] = inc;
+        if (t == 0) sel_b = -1;
+        __syncthreads();
+        if (w == 0) {
+            unsigned long long x = wsum[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned long long up = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += up;
+            }
+            wsum[lane] = x;
+        }
+        __syncthreads();
+        const unsigned long long total = wsum[31];
+        const unsigned long long want = (r < nr) ? st->resid[r] : 0ull;
+        unsigned long long cum = inc - s + (w ? wsum[w - 1] : 0ull);
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            if (cum <= want && want < cum + c[k]) { sel_b = t * PER + k; sel_cum = cum; }
+            cum += c[k];
+        }
+        __syncthreads();
+        if (t == 0) {
+            if (LEVEL == 1 && r == 0) st->count = total;
+            if (r < nr) {
+                int b = sel_b;
+                unsigned long long cm = sel_cum;
+                if (b < 0) { b = BINS - 1; cm = total - h[BINS - 1]; }
+                st->resid[r] = want - cm;
+                st->prefix[r] = (LEVEL == 1) ? (unsigned)b : ((old[r] << BITS) | (unsigned)b);
+                if (LEVEL == 3) st->result[r] = st->prefix[r];
+            }
+        }
+        __syncthreads();
     }
 }
 
