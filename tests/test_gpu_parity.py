@@ -306,6 +306,10 @@ def test_full_rate_stft_frame_major_equals_rows(eng, n):
         part = eng.stft(d[f_lo * 512 - 10:], "hann", 1024, 512, 1024, 56e6, in_origin=f_lo * 512 - 10,
                         frame_lo=f_lo, n_frames=A.shape[1] - f_lo, total_len=n)
         assert torch.equal(part, A[:, f_lo:])
+    if n > 1025:                                                       # input 8-byte aligned only: register-load path
+        odd = d[1:]
+        assert odd.data_ptr() % 16 == 8
+        assert torch.equal(eng.stft(odd, "hann", 1024, 512, 1024, 56e6), eng.stft(odd.clone(), "hann", 1024, 512, 1024, 56e6))
 
 
 # ------------------------------------------------------------------------------ fused build + STFT

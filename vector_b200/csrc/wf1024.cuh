@@ -382,6 +382,32 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
     const bool track = a.flag != nullptr;
     const unsigned long long pol = wf_policy_evict_first();
 
+    // PLAIN: the input halves (4 KB contiguous each) arrive by TMA bulk loads into the warp's staging block
+    // (unused otherwise in this mode), one half ahead: issued when the previous half has been taken, waited
+    // for through the warp's mbarrier (it lives in the unused zero block).  Needs a 16-byte aligned input.
+    const bool pl_tma = PLAIN && BULK && (reinterpret_cast<unsigned long long>(a.vec) & 15ull) == 0;
+    const unsigned pl_bar = zero_u32 + 8u * warp;
+    unsigned pl_phase = 0;
+    bool pl_primed = false;                                  // the first half of the next item is already on its way
+    if (pl_tma) {
+        if (lane == 0) mbar_init(pl_bar, 1);
+        __syncwarp();
+    }
+    auto pl_issue = [&](long long half) {                    // all lanes; the staging block has been read out
+        __syncwarp();
+        if (lane == 0) {
+            wf_fence_async();
+            mbar_expect_tx(pl_bar, 4096u);
+            tma_bulk_g2s(smem_u32(vst), a.vec + half * 512, 4096u, pl_bar);
+        }
+    };
+    auto pl_take = [&](float2 (&x)[16]) {
+        mbar_wait(pl_bar, pl_phase);
+        pl_phase ^= 1u;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) x[j] = vst[lane + 32 * j];
+    };
+
     unsigned next = 0;
     if (lane == 0) next = atomicAdd(a.ctr, 1u);
     for (;;) {
@@ -408,7 +434,11 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
 
         float2 xo[16], xn[16];
         bool live_o = true;
-        if (PLAIN) {
+        if (PLAIN && pl_tma) {
+            if (!pl_primed) pl_issue(h0);
+            pl_take(xo);
+            pl_issue(h0 + 1);                                // frame h0 exists, so does half h0 + 1
+        } else if (PLAIN) {
             const float2 *src = a.vec + h0 * 512 + lane;
 #pragma unroll
             for (int j = 0; j < 16; ++j) xo[j] = __ldcs(src + 32 * j);
@@ -423,7 +453,16 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
             const bool sv = !PLAIN && (i + 1 < cn) && (h + 1) * 512 < n_vec;      // this item stores half h + 1
             if (!fv && !sv) break;
             bool live_n = true;
-            if (PLAIN) {
+            if (PLAIN && pl_tma) {
+                pl_take(xn);
+                if (i + 1 < cn && h + 1 < a.n_frames) {
+                    pl_issue(h + 2);                         // the next frame of this item
+                } else {                                     // last frame of the item: start on the next item
+                    const long long cx = __shfl_sync(0xffffffffu, next, 0);
+                    pl_primed = cx < a.n_chunks;
+                    if (pl_primed) pl_issue(cx < a.n_big ? cx * CHUNK : a.n_big * CHUNK + (cx - a.n_big));
+                }
+            } else if (PLAIN) {
                 const float2 *src = a.vec + (h + 1) * 512 + lane;
 #pragma unroll
                 for (int j = 0; j < 16; ++j) xn[j] = __ldcs(src + 32 * j);
