@@ -19,7 +19,7 @@ spec_rows = eng.alloc_spectrogram(1024, nf)
 spec_fm = eng.alloc_spectrogram(1024, nf, frame_major=True)
 spec = spec_rows
 descs, nd = eng.make_descs(rows)
-KEYS = ("LAYOUT", "B200VEC_WF_V", "B200VEC_WF_CHUNK", "B200VEC_WF_BULK", "B200VEC_WF_TAIL", "B200VEC_FUSED_W", "B200VEC_FUSED_V", "B200VEC_PIPE", "B200VEC_FUSED_TS", "B200VEC_FUSED_ZTMA")
+KEYS = ("LAYOUT", "B200VEC_WF_TF", "B200VEC_WF_V", "B200VEC_WF_CHUNK", "B200VEC_WF_BULK", "B200VEC_WF_TAIL", "B200VEC_FUSED_W", "B200VEC_FUSED_V", "B200VEC_PIPE", "B200VEC_FUSED_TS", "B200VEC_FUSED_ZTMA")
 
 
 def run():

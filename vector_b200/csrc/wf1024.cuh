@@ -442,16 +442,16 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
             const float2 *src = a.vec + h0 * 512 + lane;
 #pragma unroll
             for (int j = 0; j < 16; ++j) xo[j] = __ldcs(src + 32 * j);
-        } else {
-            live_o = wf_build_half(a, active, cnt_l, rel0_l, 0, lane, xo, keep);
-            wf_store_half<!(DBG & 2), BULK>(a.vec, h0 * 512, n_vec, live_o, scl, lane, xo, vst, zero_u32, pol);
         }
+        // Fused mode: the loop starts one iteration early (i = -1 only places and stores the item's first
+        // half), so that the gather and the store are instantiated once — the kernel's code size sits at an
+        // instruction-cache cliff (64 KB), and the hot loop is what every warp fetches out of step.
 #pragma unroll 1
-        for (int i = 0; i < cn; ++i) {
+        for (int i = PLAIN ? 0 : -1; i < cn; ++i) {
             const long long h = h0 + i;
-            const bool fv = h < a.n_frames;                                   // frame h exists
+            const bool fv = i >= 0 && h < a.n_frames;                         // frame h exists
             const bool sv = !PLAIN && (i + 1 < cn) && (h + 1) * 512 < n_vec;      // this item stores half h + 1
-            if (!fv && !sv) break;
+            if (i >= 0 && !fv && !sv) break;
             bool live_n = true;
             if (PLAIN && pl_tma) {
                 pl_take(xn);
