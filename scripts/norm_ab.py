@@ -15,7 +15,7 @@ plan = vdist.plan_slab(N, 1, 0, 1024, 512, 1, align=512)
 nf = plan.frame_hi - plan.frame_lo
 vec = torch.empty(N, dtype=torch.complex64, device=eng.device)
 spec = eng.alloc_spectrogram(1024, nf, frame_major=True)
-KEYS = ("B200VEC_WF_TF", "B200VEC_WF_CHUNK", "B200VEC_WF_BULK", "B200VEC_WF_TAIL")
+KEYS = ("B200VEC_WF_ZW", "B200VEC_WF_TF", "B200VEC_WF_CHUNK", "B200VEC_WF_BULK", "B200VEC_WF_TAIL")
 
 
 def run():
