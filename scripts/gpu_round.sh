@@ -1,8 +1,10 @@
 #!/bin/bash
-N=${1:-2}
 mkdir -p gpurun_out
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517"
-timeout 240 $TR bench.py --gpus $N --steps 20 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err
-echo "bench rc=$?"; cut -c1-330 gpurun_out/bench_n$N.json
-timeout 240 $TR scripts/peer_check.py > gpurun_out/peer_check_n$N.txt 2>&1
-echo "peer rc=$?"; tail -4 gpurun_out/peer_check_n$N.txt
+P=$PWD/vector_b200/csrc
+for i in 1 2; do
+B200VEC_LIB=$P/libb200vec.so timeout 100 python scripts/fused_ab.py LAYOUT=fm 2>&1 | head -1
+B200VEC_LIB=$P/libb200vec_tf.so timeout 100 python scripts/fused_ab.py LAYOUT=fm LAYOUT=fm,B200VEC_WF_CHUNK=8 2>&1 | grep -v identical | head -2
+B200VEC_LIB=$P/libb200vec.so timeout 100 python scripts/norm_ab.py "" 2>&1 | head -1
+B200VEC_LIB=$P/libb200vec_tf.so timeout 100 python scripts/norm_ab.py "" B200VEC_WF_CHUNK=8 2>&1 | grep -v identical | head -2
+done
+B200VEC_LIB=$P/libb200vec_tf.so timeout 300 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "fused or peer or cfg4 or cfg5 or full_size" 2>&1 | tail -2
