@@ -185,6 +185,20 @@ __device__ __forceinline__ bool wf_build_half(const WfArgs &a, unsigned active, 
     return live;
 }
 
+// mbarrier wait for a whole warp with a warp-uniform loop condition (lane 0 polls, the result is shuffled):
+// a per-lane spin loop makes ptxas treat everything after it as possibly divergent and emit out-of-line
+// slow paths — among them a copy of the second transform — behind the __syncwarps of the main loop.
+__device__ __forceinline__ void wf_mbar_wait_warp(unsigned mbar, unsigned parity, int lane) {
+    unsigned ok;
+    do {
+        ok = 0;
+        if (lane == 0)
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                         "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(mbar), "r"(parity) : "memory");
+        ok = __shfl_sync(0xffffffffu, ok, 0);
+    } while (!ok);
+}
+
 __device__ __forceinline__ void wf_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void wf_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -402,7 +416,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         }
     };
     auto pl_take = [&](float2 (&x)[16]) {
-        mbar_wait(pl_bar, pl_phase);
+        wf_mbar_wait_warp(pl_bar, pl_phase, lane);
         pl_phase ^= 1u;
 #pragma unroll
         for (int j = 0; j < 16; ++j) x[j] = vst[lane + 32 * j];
@@ -435,7 +449,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         float2 xo[16], xn[16];
         bool live_o = true;
         if (PLAIN && pl_tma) {
-            if (!pl_primed) pl_issue(h0);
+            if (!__shfl_sync(0xffffffffu, (int)pl_primed, 0)) pl_issue(h0);   // shuffled: provably warp-uniform for ptxas
             pl_take(xo);
             pl_issue(h0 + 1);                                // frame h0 exists, so does half h0 + 1
         } else if (PLAIN) {
