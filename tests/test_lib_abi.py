@@ -66,3 +66,25 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
                 assert "ref_port" not in src and "/root/reference" not in src, f
+
+
+def test_fused_kernel_code_size_below_the_cliff():
+    """profiles/README.md, "Code-size cliff": every build whose fused wf1024_kernel instantiation exceeded
+    64 KB of SASS ran the unchanged step 40 us slower.  Keep it below, with headroom."""
+    import re, shutil, subprocess
+    from vector_b200._lib import LIB_PATH
+    if shutil.which("cuobjdump") is None or not os.path.exists(LIB_PATH):
+        pytest.skip("cuobjdump or the built library is not available")
+    sass = subprocess.run(["cuobjdump", "-sass", LIB_PATH], capture_output=True, text=True, timeout=300).stdout
+    inside, last = False, None
+    for line in sass.splitlines():
+        if "Function :" in line:
+            if inside:
+                break
+            inside = "wf1024_kernelILi4ELi0ELb1ELb0" in line
+        elif inside:
+            m = re.match(r"\s*/\*([0-9a-f]{4,6})\*/", line)
+            if m:
+                last = int(m.group(1), 16)
+    assert last is not None, "fused wf1024_kernel<4,0,true,false> not found in the library"
+    assert last + 16 <= 62 * 1024, f"fused kernel is {last + 16} bytes of SASS (cliff at 65536)"
