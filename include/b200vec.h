@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200VEC_ABI_VERSION 1
+#define B200VEC_ABI_VERSION 2
 #define B200VEC_MAX_PACKETS 32      /* descriptors per build call (reference: MAX_PACKETS = 6, unified_gui.py:41) */
 #define B200VEC_MAX_SLOTS   64      /* packet-bank slots per context */
 #define B200VEC_MAX_RANKS   8       /* order statistics per select call */
@@ -71,13 +71,21 @@ int b200vec_destroy(b200vec_ctx *ctx);
  * shift    : apply_frequency_shift (utils.py:120-127): y[n] *= exp(j*(2*pi*f)*(n/fs)),
  *            phase in fp64 from the integer packet-local index, one rounding to complex64.
  *            freq_hz == 0 commits the samples unchanged (utils.py:122-123).
- *            shift also "commits" the slot: it writes the two 16-byte-phase copies the
- *            placement kernel reads.  A slot must be committed before b200vec_build.
+ *            shift also "commits" the slot: it writes the copies the placement kernels
+ *            read.  A slot must be committed before b200vec_build.
+ * attach   : make caller-owned device memory (complex64 [len], 8-byte aligned) a committed slot
+ *            without copying it — e.g. one common period of an already built vector, which the
+ *            next launch then places like a packet of period == len (dist.build_stft_slab's
+ *            periodic tiling: the composite of unified_gui.py:1757-1769 repeats bit for bit with the
+ *            least common multiple of the packet periods).  Works with b200vec_build* and the
+ *            frame-major fused step; the memory must stay valid and unchanged while launches that
+ *            name the slot run.
  * download : committed samples back to the host (synchronises the stream). */
 int b200vec_bank_upload(b200vec_ctx *ctx, int slot, const void *src, int64_t len,
                         int src_is_device, void *stream);
 int b200vec_bank_resample(b200vec_ctx *ctx, int slot, int64_t len_out, void *stream);
 int b200vec_bank_shift(b200vec_ctx *ctx, int slot, double freq_hz, double fs_hz, void *stream);
+int b200vec_bank_attach(b200vec_ctx *ctx, int slot, const void *samples_dev, int64_t len, void *stream);
 int b200vec_bank_len(b200vec_ctx *ctx, int slot, int64_t *len_out);
 int b200vec_bank_download(b200vec_ctx *ctx, int slot, void *dst_host, int64_t len, void *stream);
 
@@ -94,6 +102,42 @@ int b200vec_bank_download(b200vec_ctx *ctx, int slot, void *dst_host, int64_t le
 int b200vec_build(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
                   int64_t slab_lo, int64_t slab_hi, void *out_dev, int mode,
                   double *maxsq_dev, void *stream);
+
+/* The normalised build in ONE launch (unified_gui.py:1778-1782 folded in): max |v|^2 over the sample
+ * ranges norm_ranges[2r] .. norm_ranges[2r+1] (n_ranges <= 4 [lo, hi) pairs, vector-absolute; ranges
+ * whose max is the max of the whole vector — all of it, or one common period of the packet trains plus
+ * head and tail), a grid barrier (cooperative launch), then the SCALE pass of b200vec_build.
+ * *maxsq_dev receives max |v|^2.  8 B per output sample of HBM traffic, nothing read. */
+int b200vec_build_norm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                       int64_t slab_lo, int64_t slab_hi, void *out_dev,
+                       const int64_t *norm_ranges, int n_ranges, double *maxsq_dev, void *stream);
+
+/* ---- scenario batch (BASELINE.json configs[4]: 256 vectors sweeping shift / period / offset) ----------
+ * The reference builds a scenario sweep by running generate_vector once per scenario
+ * (unified_gui.py:1722-1782 in a loop).  Here the whole sweep is two calls:
+ *   prepare : every packet of every scenario, pkts[first[v] .. first[v+1]) for vector v.  Each distinct
+ *             (src_slot, freq_hz) pair is shifted ONCE (apply_frequency_shift, utils.py:120-127, same
+ *             arithmetic as b200vec_bank_shift) into a batch bank owned by the context, in one launch;
+ *             src_slot names an uploaded (optionally resampled) packet, it need not be committed.
+ *             Synchronises the stream.
+ *   build   : ONE launch places, (per vector) normalises and stores all vectors:
+ *             out_dev[v * out_ld + i] = sample i of vector v, 0 <= i < total.  normalize != 0: each vector
+ *             is divided by its own max |v| (maxsq_dev: n_vectors doubles, receives max |v|^2 per vector);
+ *             the kernel finds the maxima itself (cooperative launch, grid barrier between the passes).
+ *             Independent vectors: no collective; shard a sweep over GPUs by vector. */
+typedef struct b200vec_batch_pkt {
+    int64_t start;     /* as b200vec_pkt_desc */
+    int64_t period;
+    int64_t count;
+    int32_t src_slot;  /* bank slot holding the packet BEFORE the frequency shift */
+    int32_t flags;     /* bit 0: the free-instance hint of b200vec_pkt_desc::reserved */
+    double  freq_hz;   /* this scenario's shift; 0 = none */
+} b200vec_batch_pkt;
+
+int b200vec_batch_prepare(b200vec_ctx *ctx, const b200vec_batch_pkt *pkts, const int32_t *first, int n_vectors,
+                          double fs_hz, void *stream);
+int b200vec_batch_build(b200vec_ctx *ctx, int64_t total, void *out_dev, int64_t out_ld, int normalize,
+                        double *maxsq_dev, void *stream);
 
 /* ---- spectrogram -------------------------------------------------------------------
  * scipy.signal.spectrogram(x[::stride], window, nperseg, noverlap=nperseg-hop, nfft,
@@ -182,6 +226,12 @@ int b200vec_build_stft1024_fm_norm_peer(b200vec_ctx *ctx, const b200vec_pkt_desc
                                         int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
                                         int *nonzero_flag_dev, void *stream);
 
+/* *status_host = 1 when a b200vec_build_stft1024_fm_norm_peer launch on this context gave up waiting for the
+ * other GPUs (the wait inside the kernel is bounded, ~2 s: a rank that never launched must not hang its
+ * peers); the step's output is then scaled by the local max only and must be discarded.  Reading clears
+ * the flag.  Synchronises the stream. */
+int b200vec_peer_status(b200vec_ctx *ctx, int *status_host, void *stream);
+
 /* ---- dB map and order statistics (normalize_spectrogram, utils.py:356-404) -----------
  * db      : out[i] = 10*log10(|s[i]| + floor)                      (utils.py:363-368)
  * select  : exact order statistics of a float32 array: ranks[] are 0-based positions in the
@@ -198,9 +248,35 @@ int b200vec_select_ranks(b200vec_ctx *ctx, const float *data_dev, int64_t n, int
                          const int64_t *ranks_host, int n_ranks, float *values_host,
                          void *stream);
 
-/* ---- .wv payload (mat2wv, vector_analyzer/mat_to_wv_converter.py:42-50) ---------------
- * out[2i] = (int16) trunc(re*32767), out[2i+1] = (int16) trunc(im*32767). */
-int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, int16_t *out_dev,
+/* Order statistics of a large array in two full reads instead of three per call (what
+ * normalize_spectrogram needs: the 5th percentile of the positive elements and the low / high percentiles,
+ * minimum and maximum of the dB image — dB is monotone in |S|, so all eight ranks are ranks of |S|):
+ *   begin  : 13-bit histogram of the order-preserving keys of data (|data| when use_abs) in one read;
+ *            *count_pos_host = number of elements > 0.  Synchronises the stream.
+ *   finish : exact values at ranks_host[] (0-based positions in the ascending sort of ALL n elements) —
+ *            the host picks each rank's histogram bin, one more read compacts the elements of those bins,
+ *            and the exact radix select of b200vec_select_ranks runs on the candidates only.
+ *            Same array, unchanged, as in begin.  Synchronises the stream. */
+int b200vec_select_begin(b200vec_ctx *ctx, const float *data_dev, int64_t n, int use_abs,
+                         int64_t *count_pos_host, void *stream);
+int b200vec_select_finish(b200vec_ctx *ctx, const float *data_dev, int64_t n, const int64_t *ranks_host,
+                          int n_ranks, float *values_host, void *stream);
+
+/* out_dev[i] = in_dev[i * stride], i < ceil(n_in / stride): the naive decimation sig[::factor] of
+ * create_spectrogram (utils.py:192-195), made once so that the overlapping preview frames read a compact
+ * copy. */
+int b200vec_decimate(b200vec_ctx *ctx, const void *in_dev, int64_t n_in, int64_t stride, void *out_dev, void *stream);
+
+/* ---- .wv payload (mat2wv, vector_analyzer/mat_to_wv_converter.py:28-50) ---------------
+ * quantize    : out[2i] = (int16) trunc(fl(re * pre_scale) * 32767), out[2i+1] likewise for im.  pre_scale = 1
+ *               is mat2wv(bNormalize=False), the form save_vector_wv / generate_vector use; the bNormalize
+ *               branch passes fl32(1 / max |x|) (numpy divides complex64 by a float32 scalar that way).
+ * power_stats : the level metrics of that branch for y = fl(x * pre_scale): stats_host[0] = max |y|^2,
+ *               stats_host[1] = sum of fl32(fl32(|y|)^2) accumulated in fp64 (the reference's float32
+ *               np.mean is a pairwise float32 sum: equal to ~1e-7 relative).  Synchronises the stream. */
+int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, float pre_scale, int16_t *out_dev,
+                        void *stream);
+int b200vec_power_stats(b200vec_ctx *ctx, const void *in_dev, int64_t n, float pre_scale, double *stats_host,
                         void *stream);
 
 /* ---- MAT v5 payload (save_vector, utils.py:659-670 -> scipy.io.savemat) --------------------
@@ -212,7 +288,7 @@ int b200vec_split_planes(b200vec_ctx *ctx, const void *in_dev, int64_t n, float 
 /* ---- the steps either side of the path -------------------------
  * box_energy        : detect_packet_bounds' smoothing (utils.py:813-816): smoothed[i] =
  *                     np.convolve(np.abs(x)**2, np.ones(window)/window, 'same')[i] in float64, and
- *                     *max_out_dev = smoothed.max().  window <= 1024 (the reference uses fs // 1e6).
+ *                     *max_out_dev = smoothed.max().  window <= 4096 (the reference uses fs // 1e6).
  * threshold_bounds  : first_last_host[0/1] = first / last i with smoothed[i] >= threshold
  *                     (utils.py:820-825); (n, -1) when none.  Synchronises the stream.
  * median2_rows      : scipy.ndimage.median_filter(S, size=(2, 1)) as plot_spectrogram applies it to

@@ -16,12 +16,19 @@ MAX_PACKETS = 32
 MAX_SLOTS = 64
 MAX_RANKS = 8
 BUILD_STORE, BUILD_MAXONLY, BUILD_SCALE = 0, 1, 2
+ABI_VERSION = 2
 
 
 class PktDesc(C.Structure):
     """b200vec_pkt_desc (include/b200vec.h)."""
     _fields_ = [("start", C.c_int64), ("period", C.c_int64), ("count", C.c_int64),
                 ("slot", C.c_int32), ("reserved", C.c_int32)]
+
+
+class BatchPkt(C.Structure):
+    """b200vec_batch_pkt (include/b200vec.h)."""
+    _fields_ = [("start", C.c_int64), ("period", C.c_int64), ("count", C.c_int64),
+                ("src_slot", C.c_int32), ("flags", C.c_int32), ("freq_hz", C.c_double)]
 
 
 class B200VecError(RuntimeError):
@@ -36,10 +43,21 @@ _SIGNATURES = {
     "b200vec_bank_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]),
     "b200vec_bank_resample": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_void_p]),
     "b200vec_bank_shift": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p]),
+    "b200vec_bank_attach": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
     "b200vec_bank_len": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int64)]),
     "b200vec_bank_download": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
     "b200vec_build": (C.c_int, [C.c_void_p, C.POINTER(PktDesc), C.c_int, C.c_int64, C.c_int64,
                                 C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "b200vec_build_norm": (C.c_int, [C.c_void_p, C.POINTER(PktDesc), C.c_int, C.c_int64, C.c_int64,
+                                     C.c_void_p, C.POINTER(C.c_int64), C.c_int, C.c_void_p, C.c_void_p]),
+    "b200vec_batch_prepare": (C.c_int, [C.c_void_p, C.POINTER(BatchPkt), C.POINTER(C.c_int32), C.c_int, C.c_double,
+                                        C.c_void_p]),
+    "b200vec_batch_build": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]),
+    "b200vec_peer_status": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.c_void_p]),
+    "b200vec_select_begin": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.POINTER(C.c_int64), C.c_void_p]),
+    "b200vec_select_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_int,
+                                        C.POINTER(C.c_float), C.c_void_p]),
+    "b200vec_decimate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]),
     "b200vec_stft": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int,
                                C.c_int, C.c_int, C.c_void_p, C.c_float, C.c_int64, C.c_int64,
                                C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
@@ -66,7 +84,8 @@ _SIGNATURES = {
     "b200vec_select_ranks": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int,
                                        C.POINTER(C.c_int64), C.c_int, C.POINTER(C.c_float),
                                        C.c_void_p]),
-    "b200vec_wv_quantize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "b200vec_wv_quantize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]),
+    "b200vec_power_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(C.c_double), C.c_void_p]),
     "b200vec_box_energy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200vec_threshold_bounds": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.POINTER(C.c_int64), C.c_void_p]),
     "b200vec_median2_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
@@ -92,7 +111,7 @@ def load():
         fn = getattr(lib, name)          # AttributeError if the .so does not export it
         fn.restype = res
         fn.argtypes = args
-    if lib.b200vec_abi_version() != 1:
+    if lib.b200vec_abi_version() != ABI_VERSION:
         raise B200VecError("libb200vec.so ABI version mismatch; rebuild it")
     _lib = lib
     return lib

@@ -24,9 +24,107 @@ _SLOT_SCRATCH = 63
 
 
 # ------------------------------------------------------------------------------ file formats
+_MI_DTYPES = {1: "<i1", 2: "<u1", 3: "<i2", 4: "<u2", 5: "<i4", 6: "<u4", 7: "<f4", 9: "<f8", 12: "<i8", 13: "<u8"}
+_MX_NUMERIC = {6: np.float64, 7: np.float32, 8: np.int8, 9: np.uint8, 10: np.int16, 11: np.uint16,
+               12: np.int32, 13: np.uint32, 14: np.int64, 15: np.uint64}
+
+
+def _mat5_element(buf, pos):
+    """(type, payload offset, payload bytes, offset of the next element) of the data element at pos."""
+    word = struct.unpack_from("<I", buf, pos)[0]
+    if word >> 16:                                         # small data element: 2-byte type, 2-byte size, 4 data bytes
+        return word & 0xFFFF, pos + 4, word >> 16, pos + 8
+    nbytes = struct.unpack_from("<I", buf, pos + 4)[0]
+    return word, pos + 8, nbytes, pos + 8 + (nbytes + 7) // 8 * 8
+
+
+def _read_mat5_numeric(path):
+    """Fast path of the MAT v5 reader for what the vector-build path loads (utils.py:89-105): a file of
+    uncompressed little-endian numeric arrays (real or complex; `Y`, `pre_samples`, ...).  Returns
+    {name: (real ndarray view, imag ndarray view or None, dims)} without copying sample data, or None when
+    the file holds anything else (compressed elements, cells, structs, chars, sparse, big-endian) — the
+    caller then goes through scipy.io.loadmat like the reference."""
+    try:
+        buf = np.memmap(path, dtype=np.uint8, mode="r")
+    except (OSError, ValueError):
+        return None
+    if buf.size < 136 or bytes(buf[126:128]) != b"IM" or bytes(buf[:4]) == b"\0\0\0\0":
+        return None
+    out, pos, end = {}, 128, buf.size
+    try:
+        while pos + 8 <= end:
+            mtype, off, nbytes, nxt = _mat5_element(buf, pos)
+            if mtype != 14 or nxt > end:                   # miMATRIX only (15 = zlib-compressed)
+                return None
+            p, stop = off, off + nbytes
+            t, o, nb, p = _mat5_element(buf, p)            # array flags
+            if t != 6 or nb != 8:
+                return None
+            flags = struct.unpack_from("<I", buf, o)[0]
+            klass, is_complex = flags & 0xFF, bool(flags & 0x0800)
+            if klass not in _MX_NUMERIC or flags & 0x0600:  # numeric classes only; no logical / global
+                return None
+            t, o, nb, p = _mat5_element(buf, p)            # dimensions
+            if t != 5:
+                return None
+            dims = struct.unpack_from("<%di" % (nb // 4), buf, o)
+            t, o, nb, p = _mat5_element(buf, p)            # name
+            if t != 1:
+                return None
+            name = bytes(buf[o:o + nb]).decode("latin1")
+            count = int(np.prod(dims)) if dims else 0
+            parts = []
+            for _ in range(2 if is_complex else 1):
+                t, o, nb, p = _mat5_element(buf, p)
+                if t not in _MI_DTYPES:
+                    return None
+                dt = np.dtype(_MI_DTYPES[t])
+                if nb != count * dt.itemsize:
+                    return None
+                parts.append(np.frombuffer(buf, dtype=dt, count=count, offset=o) if count else np.zeros(0, dt))
+            if p > stop + 8:
+                return None
+            out[name] = (parts[0], parts[1] if is_complex else None, dims, _MX_NUMERIC[klass])
+            pos = nxt
+    except (struct.error, ValueError, IndexError):
+        return None
+    return out if pos == end else None
+
+
+def _load_packet_fast(file_path):
+    """load_packet_info through the fast reader; None when the file needs scipy's general reader."""
+    arrays = _read_mat5_numeric(file_path)
+    if arrays is None:
+        return None
+    if "Y" in arrays:
+        key = "Y"
+    elif len(arrays) == 1:
+        key = next(iter(arrays))
+    else:
+        return None                                        # ambiguous: let the reference path raise its message
+    re, im, dims, _ = arrays[key]
+    if sum(1 for d in dims if d != 1) > 1:
+        return None                                        # a true matrix: its flatten order needs the general path
+    y = np.empty(re.shape[0], dtype=np.complex64)
+    y.real = re                                            # per-component cast to float32 == astype(complex64)
+    y.imag = im if im is not None else 0
+    pre = 0
+    if "pre_samples" in arrays:
+        pr, pi, pdims, _ = arrays["pre_samples"]
+        if pr.shape[0] != 1 or pi is not None:
+            return None
+        pre = int(pr[0])
+    return y, pre
+
+
 def load_packet_info(file_path):
     """(complex64 samples, pre_samples) — utils.py:89-105.  Key 'Y', else the single
-    non-dunder key, else ValueError; flattened; pre_samples defaults to 0."""
+    non-dunder key, else ValueError; flattened; pre_samples defaults to 0.  Plain numeric MAT v5 files
+    (what save_vector and the packet extractor write) are parsed directly from a memory map — one pass
+    from the file's planes to complex64; anything else goes through scipy.io.loadmat."""
+    fast = _load_packet_fast(file_path)
+    if fast is not None:
+        return fast
     mat = sio.loadmat(file_path, squeeze_me=True, struct_as_record=False)
     if "Y" in mat:
         data = mat["Y"]
@@ -85,25 +183,68 @@ def _mat5_file_header():
 
 def _write_mat5_vector(output_path, re_plane, im_plane, n):
     """MAT v5 file {'Y': complex single 1 x n, 'pre_samples': int64 0} written straight from the two
-    float32 planes — byte-identical to scipy.io.savemat's output after the 128-byte text header."""
+    float32 planes — byte-identical to scipy.io.savemat's output after the 128-byte text header.
+    A plane is a host array or a CUDA tensor (then it is streamed, _stream_to_file)."""
     pad = b"\0" * ((-4 * n) % 8)
-    with open(output_path, "wb") as fh:
-        fh.write(_mat5_file_header())
-        fh.write(_mat5_y_header(n))
+    with open(output_path, "wb", buffering=0) as fh:
+        fh.write(_mat5_file_header() + _mat5_y_header(n))
         for plane in (re_plane, im_plane):
             fh.write(_mat5_tag(7, 4 * n))
-            fh.write(memoryview(plane).cast("B"))
+            if isinstance(plane, torch.Tensor):
+                _stream_to_file(fh, plane)
+            else:
+                fh.write(memoryview(plane).cast("B"))
             fh.write(pad)
         fh.write(_MAT5_PRE_SAMPLES)
+
+
+_RING = {}
+_CHUNK_BYTES = 32 << 20
+
+
+def _ring(device):
+    """Two pinned staging blocks + two events per device, allocated once."""
+    key = device.index
+    if key not in _RING:
+        _RING[key] = ([torch.empty(_CHUNK_BYTES, dtype=torch.uint8).pin_memory() for _ in range(2)],
+                      [torch.cuda.Event() for _ in range(2)])
+    return _RING[key]
+
+
+def _stream_to_file(fh, dev):
+    """Write a contiguous CUDA tensor's bytes to the open file: chunked device-to-host copies into a
+    two-block pinned ring, the copy of chunk k+1 in flight (DMA engine) while chunk k is being written —
+    the save path's D2H costs no wall time beyond the file write itself."""
+    flat = dev.reshape(-1).view(torch.uint8)
+    total = flat.numel()
+    if total == 0:
+        return
+    bufs, evs = _ring(dev.device)
+    stream = torch.cuda.current_stream(dev.device)
+    n_chunks = (total + _CHUNK_BYTES - 1) // _CHUNK_BYTES
+
+    def issue(k):
+        lo = k * _CHUNK_BYTES
+        hi = min(total, lo + _CHUNK_BYTES)
+        bufs[k & 1][: hi - lo].copy_(flat[lo:hi], non_blocking=True)
+        evs[k & 1].record(stream)
+        return hi - lo
+
+    sizes = {0: issue(0)}
+    for k in range(n_chunks):
+        if k + 1 < n_chunks:
+            sizes[k + 1] = issue(k + 1)                   # block (k+1)&1 was written out one iteration ago
+        evs[k & 1].synchronize()
+        fh.write(memoryview(bufs[k & 1].numpy())[: sizes.pop(k)])
 
 
 def save_vector(vector, output_path):
     """MAT v5 {'Y': complex64 1-D, 'pre_samples': 0} — utils.py:659-670.  `vector` is a numpy array
     (the reference's argument) or a complex64 CUDA tensor.  The file is written directly in
     savemat's layout (two float32 planes) instead of through scipy's generic writer; a CUDA tensor is
-    split into its planes on the device (K7) and leaves through pinned memory.  Vectors shorter than
-    2 samples or too long for one MAT v5 element (>= 2^29 samples) go through scipy.io.savemat, which
-    then produces the very output / exception the reference produces."""
+    split into its planes on the device (K7) and streamed through a pinned ring while the file is being
+    written.  Vectors shorter than 2 samples or too long for one MAT v5 element (>= 2^29 samples) go
+    through scipy.io.savemat, which then produces the very output / exception the reference produces."""
     if isinstance(vector, torch.Tensor) and vector.is_cuda:
         dev = vector.reshape(-1)
         if dev.dtype != torch.complex64:
@@ -112,11 +253,7 @@ def save_vector(vector, output_path):
         if 2 <= n < (1 << 29):
             eng = get_engine(dev.device)
             planes = eng.split_planes(dev)
-            host = torch.empty(planes.shape, dtype=torch.float32).pin_memory()
-            host.copy_(planes, non_blocking=True)
-            torch.cuda.current_stream(dev.device).synchronize()
-            hp = host.numpy()
-            _write_mat5_vector(output_path, hp[0], hp[1], n)
+            _write_mat5_vector(output_path, planes[0], planes[1], n)
             return
         vector = dev.cpu().numpy()
     vector = np.asarray(vector)
@@ -144,25 +281,50 @@ def wv_payload_device(vector_dev, engine=None):
     return eng.wv_quantize(vector_dev)
 
 
+def wv_levels_device(dev, engine=None):
+    """mat2wv's bNormalize branch (mat_to_wv_converter.py:30-36) for a complex64 CUDA tensor:
+    (pre_scale, rms_dbfs, peak_dbfs) with pre_scale = fl32(1 / max |x|) — numpy divides a complex64 array
+    by a float32 scalar by multiplying with its float32 reciprocal — and the two header values as the
+    float32 scalars the reference formats.  max |x| is the correctly rounded float32 of the exact maximum
+    (numpy's SIMD hypot may differ in the last bit); the mean power is accumulated in fp64 (the reference's
+    float32 pairwise mean differs from it by ~1e-7 relative, < 1e-6 dB in the header)."""
+    eng = engine or get_engine(dev.device)
+    n = dev.numel()
+    mx2, _ = eng.power_stats(dev, 1.0)
+    m = np.float32(np.sqrt(mx2))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        r = np.float32(1.0) / m
+        pk2, sm = eng.power_stats(dev, float(r))
+        a = np.float32(np.sqrt(pk2))
+        peak = np.float32(-10) * np.log10(a * a)
+        rms = np.float32(-10) * np.log10(np.float32(sm / n))
+    return float(r), rms, peak
+
+
 def save_vector_wv(vector, output_path, sample_rate, normalize=False, _date=None):
     """R&S .wv writer — utils.py:672-677 -> mat2wv(vector, path, fs, bNormalize=normalize)
     (vector_analyzer/mat_to_wv_converter.py:7-65).  `vector` may be a numpy array or a
-    complex64 CUDA tensor (then only the 4 B/sample payload crosses PCIe)."""
-    if normalize:
-        raise NotImplementedError(
-            "save_vector_wv(normalize=True) (mat2wv's bNormalize branch) is not on the vector-build "
-            "path — generate_vector always passes normalize=False (unified_gui.py:1788, main.py:282)")
-    eng = get_engine()
+    complex64 CUDA tensor: quantisation (and, with normalize=True, max |x| and the level metrics) run on
+    the device, and only the 4 B/sample int16 payload crosses PCIe, streamed through a pinned ring while
+    the file is being written."""
+    eng = get_engine(vector.device) if isinstance(vector, torch.Tensor) and vector.is_cuda else get_engine()
     if isinstance(vector, torch.Tensor):
-        dev = vector.reshape(-1)
+        dev = vector.reshape(-1).to(device=eng.device, dtype=torch.complex64)
     else:
         host = np.asarray(vector).flatten().astype(np.complex64)
         dev = torch.from_numpy(host).to(eng.device)
     n = dev.numel()
-    payload = eng.wv_quantize(dev).cpu().numpy() if n else np.zeros(0, np.int16)
-    with open(output_path, "wb") as fh:
-        fh.write(wv_header(n, sample_rate, date=_date))
-        fh.write(payload.tobytes())
+    pre_scale, rms, peak = 1.0, 0.0, 0.0
+    if normalize:
+        if n == 0:
+            raise ValueError("zero-size array to reduction operation maximum which has no identity")   # np.max([])
+        print("Normalize signal")
+        pre_scale, rms, peak = wv_levels_device(dev, eng)
+    payload = eng.wv_quantize(dev, pre_scale=pre_scale) if n else None
+    with open(output_path, "wb", buffering=0) as fh:
+        fh.write(wv_header(n, sample_rate, rms, peak, date=_date))
+        if n:
+            _stream_to_file(fh, payload)
         fh.write(b"}")
 
 
@@ -198,18 +360,21 @@ compute_freq_ranges = H.compute_freq_ranges
 
 
 # ------------------------------------------------------------------------------ spectrogram
-def _run_plan(eng, x_dev, plan, flag):
+def _run_plan(eng, x_dev, plan, flag, stride):
     plan = H.resolve_plan(plan)                      # may raise ValueError like scipy would
     flag.zero_()
     S = eng.stft(x_dev, plan.window, plan.nperseg, plan.noverlap, plan.nfft, plan.fs,
-                 scaling=plan.scaling, stride=plan.factor, flag=flag)
+                 scaling=plan.scaling, stride=stride, flag=flag)
     return plan, S
 
 
 def create_spectrogram_device(sig_dev, sr, center_freq=0, max_samples=2_000_000,
                               time_resolution_us=1, adaptive_resolution=True, engine=None):
     """create_spectrogram on a complex64 CUDA tensor; returns (freqs f64, times f64, Sxx CUDA
-    float32 [nfft, frames]).  Follows utils.py:161-353 including the fallback chain."""
+    float32 [nfft, frames]).  Follows utils.py:161-353 including the fallback chain.  A decimated
+    preview (heavy signals, utils.py:192-195) gathers sig[::factor] ONCE into a compact buffer
+    (b200vec_decimate) that the overlapping frames then read — the same samples and arithmetic as
+    transforming the strided view."""
     n = sig_dev.numel()
     if n == 0:
         raise ValueError("Signal is empty")
@@ -218,18 +383,21 @@ def create_spectrogram_device(sig_dev, sr, center_freq=0, max_samples=2_000_000,
     if plan0.heavy:
         print(f"🔍 Heavy packet detected: {n:,} samples ({n/sr:.2f}s)")
         print(f"📉 Downsampled by factor {plan0.factor}: {plan0.n_dec:,} samples")
+    x, stride = sig_dev, plan0.factor
+    if stride > 1 and plan0.nperseg >= 2 * plan0.hop:            # frames overlap: read the strided samples once
+        x, stride = eng.decimate(sig_dev, stride), 1
     flag = eng._flag
     fb = H.fallback_plans(plan0)
     try:
-        plan, S = _run_plan(eng, sig_dev, plan0, flag)
-    except ValueError:
-        plan, S = _run_plan(eng, sig_dev, fb["on_error"], flag)          # utils.py:298-313
+        plan, S = _run_plan(eng, x, plan0, flag, stride)
+    except Exception:                                                    # utils.py:298-313 catches everything
+        plan, S = _run_plan(eng, x, fb["on_error"], flag, stride)
     if int(flag.item()) == 0:                                            # utils.py:316
         print("Warning: Spectrogram is all zeros, trying with reduced window size...")
         try:
-            plan, S = _run_plan(eng, sig_dev, fb["on_zero"], flag)       # :318-334
+            plan, S = _run_plan(eng, x, fb["on_zero"], flag, stride)     # :318-334
         except Exception:
-            plan, S = _run_plan(eng, sig_dev, fb["last_resort"], flag)   # :335-347
+            plan, S = _run_plan(eng, x, fb["last_resort"], flag, stride)  # :335-347
     freqs = np.fft.fftshift(plan.freqs()) * plan.factor + center_freq    # :350
     return freqs, plan.times(), S
 
@@ -294,11 +462,19 @@ def detect_packet_bounds(signal, sample_rate, threshold_ratio=0.2):
         dev = torch.from_numpy(np.ascontiguousarray(np.asarray(signal).reshape(-1).astype(np.complex64))).to(eng.device)
     n = dev.numel()
     window = max(1, int(sample_rate // 1_000_000))
-    if n == 0 or n < window or window > 1024:
-        raise ValueError("detect_packet_bounds: the signal must be at least one smoothing window "
-                         f"({window} samples, at most 1024) long")
+    if n == 0:
+        raise ValueError("zero-size array to reduction operation maximum which has no identity")   # smoothed.max()
+    if window > 4096:
+        raise ValueError(f"detect_packet_bounds: smoothing window of {window} samples (sample rate above 4 GHz)")
+    if n < window:
+        # np.convolve(energy, kernel, 'same') returns max(n, window) samples centred on the LONGER operand:
+        # the same numbers as smoothing the signal zero-padded to `window` samples from this offset
+        pad = torch.zeros(window, dtype=torch.complex64, device=eng.device)
+        off = (window - 1) // 2 - (n - 1) // 2
+        pad[off:off + n] = dev
+        dev = pad
     smoothed, max_en = eng.box_energy(dev, window)
-    head = smoothed[: max(1, n // 10)]
+    head = smoothed[: max(1, smoothed.numel() // 10)]         # len(smoothed) = max(n, window)
     srt, _ = torch.sort(head)
     m = srt.numel()
     noise = float(srt[m // 2]) if m % 2 else float((srt[m // 2 - 1] + srt[m // 2]) / 2)     # np.median
@@ -306,7 +482,7 @@ def detect_packet_bounds(signal, sample_rate, threshold_ratio=0.2):
     threshold = noise + threshold_ratio * (max_en - noise)
     first, last = eng.threshold_bounds(smoothed, threshold)
     if last < 0:
-        return 0, n
+        return 0, n                                     # (0, len(signal)), utils.py:822-823
     return first, last
 
 

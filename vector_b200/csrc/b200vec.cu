@@ -6,8 +6,11 @@
 #include "stft.cuh"
 #include "stft1024.cuh"
 #include "fused1024.cuh"
-#include "pipe1024.cuh"
+#ifdef B2_AB
+#include "pipe1024.cuh"       // warp-specialised variant, measured slower: A/B builds only
+#endif
 #include "wf1024.cuh"
+#include "span.cuh"
 #include "packet.cuh"
 #include "select.cuh"
 
@@ -17,14 +20,41 @@ thread_local std::string g_last_error;
 // K6: mat2wv quantiser (vector_analyzer/mat_to_wv_converter.py:42-50): x*32767 in float32,
 // truncation toward zero, int16 I/Q interleave.  Out-of-range values wrap modulo 2^16 like
 // the x86 cvttss2si + narrowing the reference's astype(int16) compiles to.
+// pre_scale: mat2wv's bNormalize branch divides by max |x| first (mat_to_wv_converter.py:31) — numpy's
+// complex64 / float32 scalar, i.e. a multiply by the float32 reciprocal, rounded, THEN the x32767.
 __global__ void __launch_bounds__(256)
-wv_quantize_kernel(const float2 *__restrict__ in, long long n, short2 *__restrict__ out) {
+wv_quantize_kernel(const float2 *__restrict__ in, long long n, float pre_scale, short2 *__restrict__ out) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const float2 v = __ldg(in + i);
-        const int re = __float2int_rz(v.x * 32767.0f);
-        const int im = __float2int_rz(v.y * 32767.0f);
+        const int re = __float2int_rz(__fmul_rn(__fmul_rn(v.x, pre_scale), 32767.0f));
+        const int im = __float2int_rz(__fmul_rn(__fmul_rn(v.y, pre_scale), 32767.0f));
         out[i] = make_short2((short)re, (short)im);
+    }
+}
+
+// mat2wv's level metrics (mat_to_wv_converter.py:31-35) of x * pre_scale: stats[0] = bits of max |y|^2 (exact
+// float32 products summed in fp64), stats[1] = sum over e[i] = fl32(fl32(|y|)^2) in fp64 (np.abs(signal)**2).
+__global__ void __launch_bounds__(256)
+power_stats_kernel(const float2 *__restrict__ in, long long n, float pre_scale, unsigned long long *__restrict__ stats) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    double mx = 0.0, sum = 0.0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float2 v = __ldg(in + i);
+        const float x = __fmul_rn(v.x, pre_scale), y = __fmul_rn(v.y, pre_scale);
+        const double e = (double)x * (double)x + (double)y * (double)y;
+        const float a = (float)sqrt(e);
+        mx = fmax(mx, e);
+        sum += (double)__fmul_rn(a, a);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (mx > 0.0) atomicMax(stats, (unsigned long long)__double_as_longlong(mx));
+        atomicAdd(reinterpret_cast<double *>(stats + 1), sum);
     }
 }
 
@@ -56,7 +86,9 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
-static int run_select(b200vec_ctx *ctx, const float *data, long long n, int positive_only,
+constexpr size_t kPinnedBytes = 64 * 1024;       // select state, the 13-bit histogram (32 KB + 16 B), small results
+
+static int run_select(b200vec_ctx *ctx, const float *data, long long n, int flags,
                       const int64_t *ranks, int nr, cudaStream_t st, SelState *host_state) {
     B2_CUDA(cudaMemsetAsync(ctx->hist, 0, sizeof(unsigned int) * kHistWords, st));
     SelState init;
@@ -65,12 +97,12 @@ static int run_select(b200vec_ctx *ctx, const float *data, long long n, int posi
     for (int r = 0; r < nr; ++r) init.resid[r] = (unsigned long long)ranks[r];
     sel_init<<<1, 1, 0, st>>>(ctx->hist, init);
     const unsigned grid = (unsigned)(ctx->sm_count * 8);
-    if (n > 0) sel_hist1<<<grid, kSelThreads, 0, st>>>(data, n, positive_only, ctx->hist);
+    if (n > 0) sel_hist1<<<grid, kSelThreads, 0, st>>>(data, n, flags, ctx->hist);
     sel_pick<1><<<1, kPickThreads, 0, st>>>(ctx->hist);
     if (nr > 0 && n > 0) {
-        sel_histN<2><<<grid, kSelThreads, (size_t)nr * kBins2 * 4, st>>>(data, n, positive_only, ctx->hist);
+        sel_histN<2><<<grid, kSelThreads, (size_t)nr * kBins2 * 4, st>>>(data, n, flags, ctx->hist);
         sel_pick<2><<<1, kPickThreads, 0, st>>>(ctx->hist);
-        sel_histN<3><<<grid, kSelThreads, (size_t)nr * kBins3 * 4, st>>>(data, n, positive_only, ctx->hist);
+        sel_histN<3><<<grid, kSelThreads, (size_t)nr * kBins3 * 4, st>>>(data, n, flags, ctx->hist);
         sel_pick<3><<<1, kPickThreads, 0, st>>>(ctx->hist);
     }
     B2_CUDA(cudaGetLastError());
@@ -108,14 +140,18 @@ int b200vec_create(int device, b200vec_ctx **out) {
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
     B2_CUDA(cudaMalloc(&ctx->hist, sizeof(unsigned int) * kHistWords));
-    B2_CUDA(cudaMallocHost(&ctx->pinned, 4096));
+    B2_CUDA(cudaMallocHost(&ctx->pinned, kPinnedBytes));
+    B2_CUDA(cudaMalloc(&ctx->top_hist, kTopBins * sizeof(unsigned int) + 2 * sizeof(unsigned long long)));
     B2_CUDA(cudaFuncSetAttribute(sel_histN<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  B200VEC_MAX_RANKS * kBins2 * 4));
     B2_CUDA(cudaFuncSetAttribute(sel_histN<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  B200VEC_MAX_RANKS * kBins3 * 4));
     B2_CUDA(cudaFuncSetAttribute(stft_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  200 * 1024));
-    if (stft1024_setup() || fused1024_setup() || pipe1024_setup() || wf1024_setup()) { delete ctx; return 1; }
+    if (stft1024_setup() || fused1024_setup() || wf1024_setup() || span_setup()) { delete ctx; return 1; }
+#ifdef B2_AB
+    if (pipe1024_setup()) { delete ctx; return 1; }
+#endif
     *out = ctx;
     return 0;
 }
@@ -133,6 +169,12 @@ int b200vec_destroy(b200vec_ctx *ctx) {
     if (ctx->hist) cudaFree(ctx->hist);
     if (ctx->zeros) cudaFree(ctx->zeros);
     if (ctx->wf_ctr) cudaFree(ctx->wf_ctr);
+    if (ctx->sp_ctr) cudaFree(ctx->sp_ctr);
+    if (ctx->top_hist) cudaFree(ctx->top_hist);
+    if (ctx->cand.ptr) cudaFree(ctx->cand.ptr);
+    if (ctx->batch.bank.ptr) cudaFree(ctx->batch.bank.ptr);
+    if (ctx->batch.tables.ptr) cudaFree(ctx->batch.tables.ptr);
+    if (ctx->batch.pin) cudaFreeHost(ctx->batch.pin);
     if (ctx->slot_max) cudaFree(ctx->slot_max);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     delete ctx;
@@ -194,6 +236,7 @@ int b200vec_bank_shift(b200vec_ctx *ctx, int slot, double freq_hz, double fs_hz,
     const int64_t per = ((sl.cap_store + 1) & ~1LL) + 2 * kBankPad + 2;
     B2_CUDA(cudaMemsetAsync(sl.store, 0, (size_t)(4 * per) * sizeof(float2), st));
     sl.per = per;
+    sl.external = false;
     sl.a = sl.store + kBankPad;                 // cudaMalloc is 256-byte aligned, kBankPad is even -> 16-byte aligned
     sl.b = sl.store + per + kBankPad + 1;       // per is even -> 8 mod 16
     // the reference forms the phase as ((2j*pi)*f)*t: w = fl(fl(2*pi)*f)   (utils.py:126)
@@ -230,17 +273,9 @@ int b200vec_bank_download(b200vec_ctx *ctx, int slot, void *dst_host, int64_t le
 }
 
 // ---------------------------------------------------------------------------------------
-int b200vec_build(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
-                  int64_t slab_lo, int64_t slab_hi, void *out_dev, int mode,
-                  double *maxsq_dev, void *stream) {
-    B2_REQUIRE(ctx, "ctx is NULL");
-    B2_REQUIRE(n_pkts >= 0 && n_pkts <= B200VEC_MAX_PACKETS, "too many packets");
-    B2_REQUIRE(n_pkts == 0 || descs, "descs is NULL");
-    B2_REQUIRE(slab_lo >= 0 && slab_hi >= slab_lo, "bad slab");
-    B2_REQUIRE(mode == B200VEC_BUILD_MAXONLY || out_dev || slab_hi == slab_lo, "out_dev is NULL");
-    B2_REQUIRE(mode == B200VEC_BUILD_STORE || maxsq_dev, "maxsq_dev is NULL");
-    B2_REQUIRE(((uintptr_t)out_dev & 15) == 0, "out_dev must be 16-byte aligned");
-    PlaceArgs args;
+static int fill_place_args(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                           int64_t slab_lo, int64_t slab_hi, PlaceArgs &args, int *slot_of = nullptr,
+                           bool need_copy_b = false) {
     memset(&args, 0, sizeof(args));
     args.lo = slab_lo; args.hi = slab_hi;
     int np = 0;
@@ -249,17 +284,219 @@ int b200vec_build(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
         B2_REQUIRE(d.slot >= 0 && d.slot < B200VEC_MAX_SLOTS, "descriptor slot out of range");
         const BankSlot &sl = ctx->slots[d.slot];
         B2_REQUIRE(sl.len > 0, "descriptor names an uncommitted bank slot");
+        B2_REQUIRE(!need_copy_b || !sl.external, "attached (caller-owned) bank slots work with the frame-major / vector-only builds");
         B2_REQUIRE(d.period > 0, "period must be positive");
         B2_REQUIRE(d.start >= 0 && d.count >= 0, "negative start/count");
         if (d.count == 0) continue;
+        if (slot_of) slot_of[np] = d.slot;
         PlaceDesc &p = args.d[np++];
         p.start = d.start; p.period = d.period; p.count = d.count;
         p.len = (int)sl.len; p.a = sl.a; p.b = sl.b;
         p.free_inst = d.reserved & 1; p.pmax = ctx->slot_max + d.slot;
     }
     args.np = np;
+    return 0;
+}
+
+static int build_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts, int64_t slab_lo, int64_t slab_hi,
+                      void *out_dev, int mode, const int64_t *norm_ranges, int n_ranges, double *maxsq_dev,
+                      void *stream) {
+    B2_REQUIRE(ctx, "ctx is NULL");
+    B2_REQUIRE(n_pkts >= 0 && n_pkts <= B200VEC_MAX_PACKETS, "too many packets");
+    B2_REQUIRE(n_pkts == 0 || descs, "descs is NULL");
+    B2_REQUIRE(slab_lo >= 0 && slab_hi >= slab_lo, "bad slab");
+    B2_REQUIRE(mode == B200VEC_BUILD_MAXONLY || out_dev || slab_hi == slab_lo, "out_dev is NULL");
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || maxsq_dev, "maxsq_dev is NULL");
+    B2_REQUIRE(((uintptr_t)out_dev & 15) == 0, "out_dev must be 16-byte aligned");
+    SpanArgs a;
+    memset(&a, 0, sizeof(a));
+    if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place)) return 1;
+    a.n_vec = 1; a.lo = slab_lo; a.hi = slab_hi;
+    a.out = (float2 *)out_dev; a.out_ld = 0;
+    a.maxsq = reinterpret_cast<unsigned long long *>(maxsq_dev);
+    a.mode = mode;
+    if (mode == B200VEC_BUILD_MAXONLY) {
+        a.n_norm = 1; a.norm_lo[0] = slab_lo; a.norm_hi[0] = slab_hi;
+        if (slab_hi == slab_lo) return 0;
+    } else if (mode == kSpNorm) {
+        B2_REQUIRE(n_ranges >= 0 && n_ranges <= kWfMaxNormRanges && (n_ranges == 0 || norm_ranges), "bad norm ranges");
+        for (int r = 0; r < n_ranges; ++r) {
+            const int64_t lo = norm_ranges[2 * r], hi = norm_ranges[2 * r + 1];
+            B2_REQUIRE(lo >= 0 && hi >= lo, "bad norm range");
+            if (hi == lo) continue;
+            a.norm_lo[a.n_norm] = lo; a.norm_hi[a.n_norm] = hi; ++a.n_norm;
+        }
+    }
     DeviceGuard g(ctx->device);
-    return launch_place(ctx, args, (float2 *)out_dev, maxsq_dev, mode, (cudaStream_t)stream);
+#ifdef B2_AB
+    if (mode != kSpNorm && ab_env("B200VEC_PLACE")) {      // round-1 kernel: needs both bank copies
+        PlaceArgs pa;
+        if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, pa, nullptr, true)) return 1;
+        return launch_place(ctx, pa, (float2 *)out_dev, maxsq_dev, mode, (cudaStream_t)stream);
+    }
+#endif
+    if (mode == kSpNorm) B2_CUDA(cudaMemsetAsync(maxsq_dev, 0, sizeof(double), (cudaStream_t)stream));
+    return launch_span(ctx, a, (cudaStream_t)stream);
+}
+
+int b200vec_build(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                  int64_t slab_lo, int64_t slab_hi, void *out_dev, int mode,
+                  double *maxsq_dev, void *stream) {
+    B2_REQUIRE(mode == B200VEC_BUILD_STORE || mode == B200VEC_BUILD_MAXONLY || mode == B200VEC_BUILD_SCALE, "unknown mode");
+    return build_impl(ctx, descs, n_pkts, slab_lo, slab_hi, out_dev, mode, nullptr, 0, maxsq_dev, stream);
+}
+
+int b200vec_build_norm(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
+                       int64_t slab_lo, int64_t slab_hi, void *out_dev,
+                       const int64_t *norm_ranges, int n_ranges, double *maxsq_dev, void *stream) {
+    return build_impl(ctx, descs, n_pkts, slab_lo, slab_hi, out_dev, kSpNorm, norm_ranges, n_ranges, maxsq_dev, stream);
+}
+
+int b200vec_bank_attach(b200vec_ctx *ctx, int slot, const void *samples_dev, int64_t len, void *stream) {
+    B2_REQUIRE(ctx && samples_dev, "NULL argument");
+    B2_REQUIRE(slot >= 0 && slot < B200VEC_MAX_SLOTS, "slot out of range");
+    B2_REQUIRE(len > 0 && len < (1LL << 31) - 2 * kTile, "packet length must be in (0, 2^31)");
+    B2_REQUIRE(((uintptr_t)samples_dev & 7) == 0, "samples must be 8-byte aligned");
+    DeviceGuard g(ctx->device);
+    BankSlot &sl = ctx->slots[slot];
+    if (!ctx->slot_max) B2_CUDA(cudaMalloc(&ctx->slot_max, sizeof(unsigned long long) * B200VEC_MAX_SLOTS));
+    B2_CUDA(cudaMemsetAsync(ctx->slot_max + slot, 0, sizeof(unsigned long long), (cudaStream_t)stream));
+    sl.a = const_cast<float2 *>((const float2 *)samples_dev);
+    sl.b = nullptr;
+    sl.external = true;
+    sl.len = len;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// scenario batch (BASELINE.json configs[4]; the loop of unified_gui.py:1722-1782 once per scenario)
+int b200vec_batch_prepare(b200vec_ctx *ctx, const b200vec_batch_pkt *pkts, const int32_t *first, int n_vectors,
+                          double fs_hz, void *stream) {
+    B2_REQUIRE(ctx && first && n_vectors >= 1, "NULL argument or empty batch");
+    B2_REQUIRE(first[0] == 0, "first[0] must be 0");
+    const int n_pk = first[n_vectors];
+    B2_REQUIRE(n_pk == 0 || pkts, "pkts is NULL");
+    int stride = 1;
+    for (int v = 0; v < n_vectors; ++v) {
+        const int c = first[v + 1] - first[v];
+        B2_REQUIRE(c >= 0 && c <= B200VEC_MAX_PACKETS, "packets per vector out of range");
+        if (c > stride) stride = c;
+    }
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    BatchState &bs = ctx->batch;
+    // distinct (source slot, shift) pairs -> shift jobs
+    std::map<std::pair<int, unsigned long long>, int> job_of;
+    std::vector<int> pk_job(n_pk);
+    std::vector<long long> job_off, job_len;
+    std::vector<double> job_freq;
+    std::vector<int> job_slot;
+    long long bank_samples = 0;
+    for (int i = 0; i < n_pk; ++i) {
+        const b200vec_batch_pkt &q = pkts[i];
+        B2_REQUIRE(q.src_slot >= 0 && q.src_slot < B200VEC_MAX_SLOTS, "source slot out of range");
+        const BankSlot &sl = ctx->slots[q.src_slot];
+        B2_REQUIRE(sl.len_raw > 0 && sl.raw, "source slot is empty (b200vec_bank_upload it first)");
+        B2_REQUIRE(q.period > 0, "period must be positive");
+        B2_REQUIRE(q.start >= 0 && q.count >= 0, "negative start/count");
+        unsigned long long fb;
+        const double f = q.freq_hz == 0.0 ? 0.0 : q.freq_hz;          // -0.0 and 0.0 are the same job
+        memcpy(&fb, &f, 8);
+        auto key = std::make_pair(q.src_slot, fb);
+        auto it = job_of.find(key);
+        if (it == job_of.end()) {
+            const int j = (int)job_off.size();
+            job_of[key] = j;
+            job_off.push_back(bank_samples); job_len.push_back(sl.len_raw); job_freq.push_back(f); job_slot.push_back(q.src_slot);
+            bank_samples += (sl.len_raw + 1) & ~1LL;                  // every packet starts on a 16-byte boundary
+            pk_job[i] = j;
+        } else {
+            pk_job[i] = it->second;
+        }
+    }
+    const int n_jobs = (int)job_off.size();
+    B2_REQUIRE(n_jobs <= 65535, "too many distinct (packet, shift) pairs for one batch");
+    const size_t b_desc = (size_t)n_vectors * stride * sizeof(PlaceDesc);
+    const size_t b_np = ((size_t)n_vectors * sizeof(int) + 15) & ~(size_t)15;
+    const size_t b_jobs = (size_t)(n_jobs > 0 ? n_jobs : 1) * sizeof(ShiftJob);
+    const size_t b_pmax = (size_t)(n_jobs > 0 ? n_jobs : 1) * sizeof(unsigned long long);
+    const size_t b_tables = b_desc + b_np + b_jobs + b_pmax;
+    if (bs.bank.bytes < (size_t)bank_samples * sizeof(float2) || bs.tables.bytes < b_tables || bs.pin_bytes < b_tables)
+        B2_CUDA(cudaStreamSynchronize(st));                            // nothing in flight reads the buffers being replaced
+    if (ensure_scratch(bs.bank, (size_t)(bank_samples > 0 ? bank_samples : 1) * sizeof(float2))) return 1;
+    if (ensure_scratch(bs.tables, b_tables)) return 1;
+    if (bs.pin_bytes < b_tables) {
+        if (bs.pin) cudaFreeHost(bs.pin);
+        bs.pin = nullptr; bs.pin_bytes = 0;
+        B2_CUDA(cudaMallocHost(&bs.pin, b_tables));
+        bs.pin_bytes = b_tables;
+    }
+    char *hp = (char *)bs.pin, *dp = (char *)bs.tables.ptr;
+    PlaceDesc *h_desc = (PlaceDesc *)hp;
+    int *h_np = (int *)(hp + b_desc);
+    ShiftJob *h_jobs = (ShiftJob *)(hp + b_desc + b_np);
+    unsigned long long *h_pmax = (unsigned long long *)(hp + b_desc + b_np + b_jobs);
+    unsigned long long *d_pmax = (unsigned long long *)(dp + b_desc + b_np + b_jobs);
+    float2 *bank = (float2 *)bs.bank.ptr;
+    memset(hp, 0, b_tables);
+    long long max_len = 1;
+    for (int j = 0; j < n_jobs; ++j) {
+        const BankSlot &sl = ctx->slots[job_slot[j]];
+        h_jobs[j].src = sl.raw; h_jobs[j].dst = bank + job_off[j]; h_jobs[j].pmax = d_pmax + j;
+        h_jobs[j].len = job_len[j];
+        h_jobs[j].w = (2.0 * M_PI) * job_freq[j];                      // ((2j*pi)*f) as utils.py:126 forms it
+        h_jobs[j].do_shift = job_freq[j] != 0.0 ? 1 : 0;
+        h_pmax[j] = 0;
+        if (job_len[j] > max_len) max_len = job_len[j];
+    }
+    for (int v = 0; v < n_vectors; ++v) {
+        int np = 0;
+        for (int i = first[v]; i < first[v + 1]; ++i) {
+            const b200vec_batch_pkt &q = pkts[i];
+            if (q.count == 0) continue;
+            PlaceDesc &p = h_desc[(size_t)v * stride + np++];
+            p.start = q.start; p.period = q.period; p.count = q.count;
+            p.len = (int)job_len[pk_job[i]];
+            p.free_inst = q.flags & 1;
+            p.pmax = d_pmax + pk_job[i];
+            p.a = bank + job_off[pk_job[i]];
+            p.b = nullptr;
+        }
+        h_np[v] = np;
+    }
+    B2_CUDA(cudaMemcpyAsync(dp, hp, b_tables, cudaMemcpyHostToDevice, st));
+    if (n_jobs > 0) {
+        long long gx = (max_len + 255) / 256;
+        if (gx > 64) gx = 64;
+        batch_shift_kernel<<<dim3((unsigned)gx, (unsigned)n_jobs), 256, 0, st>>>((const ShiftJob *)(dp + b_desc + b_np), fs_hz);
+        B2_CUDA(cudaGetLastError());
+    }
+    B2_CUDA(cudaStreamSynchronize(st));                                // the pinned staging block may be reused now
+    bs.descs = dp; bs.np = (const int *)(dp + b_desc);
+    bs.n_vec = n_vectors; bs.pk_stride = stride; bs.n_jobs = n_jobs;
+    return 0;
+}
+
+int b200vec_batch_build(b200vec_ctx *ctx, int64_t total, void *out_dev, int64_t out_ld, int normalize,
+                        double *maxsq_dev, void *stream) {
+    B2_REQUIRE(ctx, "ctx is NULL");
+    const BatchState &bs = ctx->batch;
+    B2_REQUIRE(bs.n_vec > 0 && bs.descs, "no prepared batch (call b200vec_batch_prepare first)");
+    B2_REQUIRE(total >= 0 && (total == 0 || out_dev), "bad arguments");
+    B2_REQUIRE(out_ld >= total && (out_ld & 1) == 0 && ((uintptr_t)out_dev & 15) == 0,
+               "out_ld >= total, even, and a 16-byte aligned base");
+    B2_REQUIRE(!normalize || maxsq_dev, "maxsq_dev is NULL");
+    if (total == 0) return 0;
+    SpanArgs a;
+    memset(&a, 0, sizeof(a));
+    a.gdesc = (const PlaceDesc *)bs.descs; a.gnp = bs.np; a.n_vec = bs.n_vec; a.pk_stride = bs.pk_stride;
+    a.lo = 0; a.hi = total; a.out = (float2 *)out_dev; a.out_ld = out_ld;
+    a.maxsq = reinterpret_cast<unsigned long long *>(maxsq_dev);
+    a.mode = normalize ? kSpNorm : B200VEC_BUILD_STORE;
+    if (normalize) { a.n_norm = 1; a.norm_lo[0] = 0; a.norm_hi[0] = total; }
+    DeviceGuard g(ctx->device);
+    if (normalize) B2_CUDA(cudaMemsetAsync(maxsq_dev, 0, sizeof(double) * bs.n_vec, (cudaStream_t)stream));
+    return launch_span(ctx, a, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -302,29 +539,6 @@ int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_
 }
 
 // ---------------------------------------------------------------------------------------
-static int fill_place_args(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
-                           int64_t slab_lo, int64_t slab_hi, PlaceArgs &args, int *slot_of = nullptr) {
-    memset(&args, 0, sizeof(args));
-    args.lo = slab_lo; args.hi = slab_hi;
-    int np = 0;
-    for (int i = 0; i < n_pkts; ++i) {
-        const b200vec_pkt_desc &d = descs[i];
-        B2_REQUIRE(d.slot >= 0 && d.slot < B200VEC_MAX_SLOTS, "descriptor slot out of range");
-        const BankSlot &sl = ctx->slots[d.slot];
-        B2_REQUIRE(sl.len > 0, "descriptor names an uncommitted bank slot");
-        B2_REQUIRE(d.period > 0, "period must be positive");
-        B2_REQUIRE(d.start >= 0 && d.count >= 0, "negative start/count");
-        if (d.count == 0) continue;
-        if (slot_of) slot_of[np] = d.slot;
-        PlaceDesc &p = args.d[np++];
-        p.start = d.start; p.period = d.period; p.count = d.count;
-        p.len = (int)sl.len; p.a = sl.a; p.b = sl.b;
-        p.free_inst = d.reserved & 1; p.pmax = ctx->slot_max + d.slot;
-    }
-    args.np = np;
-    return 0;
-}
-
 int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts,
                            int64_t slab_lo, int64_t slab_hi, void *vec_out_dev, int mode,
                            double *maxsq_dev, const float *window_dev, float scale,
@@ -345,7 +559,7 @@ int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
     B2_REQUIRE(n_frames * kFMaxHop <= slab_hi - slab_lo + kFMaxHop - 1, "frames must start inside the slab");
     FArgs a;
     int slot_of[B200VEC_MAX_PACKETS];
-    if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place, slot_of)) return 1;
+    if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place, slot_of, true)) return 1;
     DeviceGuard g(ctx->device);
     if (!ctx->zeros) {                                     // TMA source for the uncovered part of a span
         B2_CUDA(cudaMalloc(&ctx->zeros, FL<16>::kSpan * sizeof(float2)));
@@ -375,7 +589,9 @@ int b200vec_build_stft1024(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
     a.frame_lo = frame_lo; a.n_frames = n_frames; a.out = spec_out_dev; a.out_ld = out_ld;
     a.flag = nonzero_flag_dev;
     if (get_tw1024(ctx, &a.tw)) return 1;
+#ifdef B2_AB
     if (pipe1024_enabled()) return launch_pipe1024<true>(ctx, a, n_frames, slab_hi - slab_lo, (cudaStream_t)stream);
+#endif
     return launch_tile1024<true>(ctx, a, n_frames, slab_hi - slab_lo, (cudaStream_t)stream);
 }
 
@@ -513,7 +729,7 @@ int b200vec_select_count(b200vec_ctx *ctx, const float *data_dev, int64_t n, int
     B2_REQUIRE(ctx && count_host && (n == 0 || data_dev), "NULL argument");
     DeviceGuard g(ctx->device);
     SelState s;
-    if (run_select(ctx, data_dev, n, positive_only, nullptr, 0, (cudaStream_t)stream, &s)) return 1;
+    if (run_select(ctx, data_dev, n, positive_only ? 1 : 0, nullptr, 0, (cudaStream_t)stream, &s)) return 1;
     *count_host = (int64_t)s.count;
     return 0;
 }
@@ -526,7 +742,7 @@ int b200vec_select_ranks(b200vec_ctx *ctx, const float *data_dev, int64_t n, int
     B2_REQUIRE(n > 0, "empty input");
     DeviceGuard g(ctx->device);
     SelState s;
-    if (run_select(ctx, data_dev, n, positive_only, ranks_host, n_ranks, (cudaStream_t)stream, &s))
+    if (run_select(ctx, data_dev, n, positive_only ? 1 : 0, ranks_host, n_ranks, (cudaStream_t)stream, &s))
         return 1;
     for (int r = 0; r < n_ranks; ++r) {
         B2_REQUIRE(ranks_host[r] >= 0 && (unsigned long long)ranks_host[r] < s.count,
@@ -537,7 +753,141 @@ int b200vec_select_ranks(b200vec_ctx *ctx, const float *data_dev, int64_t n, int
 }
 
 // ---------------------------------------------------------------------------------------
-int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, int16_t *out_dev,
+// Fast order statistics (select.cuh, "Fast path"): begin = 13-bit top histogram (one read), finish = bin pick on
+// the host, compaction of the bins in question (one read), exact select on the candidates.
+int b200vec_select_begin(b200vec_ctx *ctx, const float *data_dev, int64_t n, int use_abs,
+                         int64_t *count_pos_host, void *stream) {
+    B2_REQUIRE(ctx && (n == 0 || data_dev), "NULL argument");
+    B2_REQUIRE(n >= 0, "negative length");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    TopState &ts = ctx->top;
+    ts.data = nullptr; ts.n = -1;
+    const size_t bytes = kTopBins * sizeof(unsigned int) + 2 * sizeof(unsigned long long);
+    B2_CUDA(cudaMemsetAsync(ctx->top_hist, 0, bytes, st));
+    if (n > 0) {
+        long long grid = (n / 4 + kSelThreads - 1) / kSelThreads + 1;
+        const long long cap = (long long)ctx->sm_count * 4;
+        if (grid > cap) grid = cap;
+        sel_top_kernel<<<(unsigned)grid, kSelThreads, 0, st>>>(data_dev, n, use_abs ? 1 : 0, ctx->top_hist,
+                                                               reinterpret_cast<unsigned long long *>(ctx->top_hist + kTopBins));
+        B2_CUDA(cudaGetLastError());
+    }
+    B2_CUDA(cudaMemcpyAsync(ctx->pinned, ctx->top_hist, bytes, cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    const unsigned int *h = reinterpret_cast<const unsigned int *>(ctx->pinned);
+    ts.hist.assign(h, h + kTopBins);
+    memcpy(&ts.n_poszero, h + kTopBins, sizeof(unsigned long long));
+    ts.data = data_dev; ts.n = n; ts.use_abs = use_abs ? 1 : 0;
+    if (count_pos_host) {
+        unsigned long long pos = 0;
+        for (unsigned b = kTopZeroBin; b < (unsigned)kTopBins; ++b) pos += ts.hist[b];   // +0 is not in the histogram
+        *count_pos_host = (int64_t)pos;
+    }
+    return 0;
+}
+
+int b200vec_select_finish(b200vec_ctx *ctx, const float *data_dev, int64_t n, const int64_t *ranks_host,
+                          int n_ranks, float *values_host, void *stream) {
+    B2_REQUIRE(ctx && data_dev && ranks_host && values_host, "NULL argument");
+    B2_REQUIRE(n_ranks >= 1 && n_ranks <= B200VEC_MAX_RANKS, "n_ranks out of range");
+    TopState &ts = ctx->top;
+    B2_REQUIRE(ts.data == data_dev && ts.n == n && n > 0, "b200vec_select_begin was not called on this array");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    // ascending order of all elements: bins below the zero bin (negative keys), the +0 block, the bins from the zero bin up
+    unsigned long long below_zero = 0;
+    for (unsigned b = 0; b < kTopZeroBin; ++b) below_zero += ts.hist[b];
+    int bin_of[B200VEC_MAX_RANKS];
+    unsigned long long resid[B200VEC_MAX_RANKS];
+    SelBins sel;
+    memset(&sel, 0, sizeof(sel));
+    for (int r = 0; r < n_ranks; ++r) {
+        B2_REQUIRE(ranks_host[r] >= 0 && ranks_host[r] < n, "rank outside the array");
+        unsigned long long want = (unsigned long long)ranks_host[r];
+        bin_of[r] = -1;
+        unsigned b0 = 0, b1 = kTopZeroBin;
+        if (want >= below_zero) {
+            if (want < below_zero + ts.n_poszero) { values_host[r] = 0.0f; continue; }     // inside the +0 block
+            want -= below_zero + ts.n_poszero;
+            b0 = kTopZeroBin; b1 = kTopBins;
+        }
+        unsigned long long cum = 0;
+        for (unsigned b = b0; b < b1; ++b) {
+            if (want < cum + ts.hist[b]) { bin_of[r] = (int)b; resid[r] = want - cum; break; }
+            cum += ts.hist[b];
+        }
+        B2_REQUIRE(bin_of[r] >= 0, "histogram does not cover the rank (array changed since b200vec_select_begin?)");
+        bool seen = false;
+        for (int q = 0; q < sel.n; ++q) seen = seen || sel.bin[q] == (unsigned)bin_of[r];
+        if (!seen) sel.bin[sel.n++] = (unsigned)bin_of[r];
+    }
+    if (sel.n == 0) return 0;
+    for (int i = 1; i < sel.n; ++i)                                   // ascending bins = ascending values
+        for (int j = i; j > 0 && sel.bin[j - 1] > sel.bin[j]; --j) { const unsigned t = sel.bin[j]; sel.bin[j] = sel.bin[j - 1]; sel.bin[j - 1] = t; }
+    unsigned long long pop = 0, before[B200VEC_MAX_RANKS];
+    for (int i = 0; i < sel.n; ++i) { before[i] = pop; pop += ts.hist[sel.bin[i]]; }
+    int64_t sub_ranks[B200VEC_MAX_RANKS];
+    int sub_of[B200VEC_MAX_RANKS], n_sub = 0;
+    const unsigned long long cap_max = (unsigned long long)(n / 8 > (1 << 20) ? n / 8 : (1 << 20));
+    SelState state;
+    if (pop <= cap_max) {
+        if (ctx->cand.bytes < pop * sizeof(float)) {
+            B2_CUDA(cudaStreamSynchronize(st));
+            if (ensure_scratch(ctx->cand, (size_t)(pop + pop / 4 + 1024) * sizeof(float))) return 1;
+        }
+        unsigned long long *cnt = reinterpret_cast<unsigned long long *>(ctx->top_hist + kTopBins) + 1;
+        B2_CUDA(cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), st));
+        const unsigned grid = (unsigned)(ctx->sm_count * 8);
+        sel_compact_kernel<<<grid, kSelThreads, 0, st>>>(data_dev, n, ts.use_abs, sel, (float *)ctx->cand.ptr, pop, cnt);
+        B2_CUDA(cudaGetLastError());
+        for (int r = 0; r < n_ranks; ++r) {
+            if (bin_of[r] < 0) continue;
+            int i = 0;
+            while (sel.bin[i] != (unsigned)bin_of[r]) ++i;
+            sub_ranks[n_sub] = (int64_t)(before[i] + resid[r]); sub_of[n_sub++] = r;
+        }
+        if (run_select(ctx, (const float *)ctx->cand.ptr, (long long)pop, 0, sub_ranks, n_sub, st, &state)) return 1;
+        B2_REQUIRE(state.count == pop, "candidate count differs from the histogram (array changed since b200vec_select_begin?)");
+    } else {                                                          // a heavily repeated value: 3-level select on the whole array
+        for (int r = 0; r < n_ranks; ++r) {
+            if (bin_of[r] < 0) continue;
+            sub_ranks[n_sub] = ranks_host[r]; sub_of[n_sub++] = r;
+        }
+        if (run_select(ctx, data_dev, n, ts.use_abs ? 2 : 0, sub_ranks, n_sub, st, &state)) return 1;
+    }
+    for (int i = 0; i < n_sub; ++i) values_host[sub_of[i]] = key2f(state.result[i]);
+    return 0;
+}
+
+int b200vec_decimate(b200vec_ctx *ctx, const void *in_dev, int64_t n_in, int64_t stride, void *out_dev, void *stream) {
+    B2_REQUIRE(ctx && n_in >= 0 && stride >= 1 && (n_in == 0 || (in_dev && out_dev)), "bad arguments");
+    const long long n_out = (n_in + stride - 1) / stride;
+    if (n_out == 0) return 0;
+    DeviceGuard g(ctx->device);
+    long long grid = (n_out + 255) / 256;
+    const long long cap = (long long)ctx->sm_count * 16;
+    if (grid > cap) grid = cap;
+    decimate_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>((const float2 *)in_dev, n_out, stride, (float2 *)out_dev);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int b200vec_peer_status(b200vec_ctx *ctx, int *status_host, void *stream) {
+    B2_REQUIRE(ctx && status_host, "NULL argument");
+    *status_host = 0;
+    if (!ctx->wf_ctr) return 0;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    B2_CUDA(cudaMemcpyAsync(ctx->pinned, ctx->wf_ctr + 10, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    *status_host = (int)*reinterpret_cast<unsigned int *>(ctx->pinned);
+    if (*status_host) B2_CUDA(cudaMemsetAsync(ctx->wf_ctr + 10, 0, sizeof(unsigned int), st));   // reading clears it
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, float pre_scale, int16_t *out_dev,
                         void *stream) {
     B2_REQUIRE(ctx && (n == 0 || (in_dev && out_dev)), "NULL argument");
     if (n == 0) return 0;
@@ -546,12 +896,32 @@ int b200vec_wv_quantize(b200vec_ctx *ctx, const void *in_dev, int64_t n, int16_t
     const long long cap = (long long)ctx->sm_count * 16;
     if (grid > cap) grid = cap;
     wv_quantize_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(
-        (const float2 *)in_dev, n, (short2 *)out_dev);
+        (const float2 *)in_dev, n, pre_scale, (short2 *)out_dev);
     B2_CUDA(cudaGetLastError());
     return 0;
 }
 
-#ifdef B2_PIPE_TIMING
+int b200vec_power_stats(b200vec_ctx *ctx, const void *in_dev, int64_t n, float pre_scale, double *stats_host,
+                        void *stream) {
+    B2_REQUIRE(ctx && stats_host && n >= 0 && (n == 0 || in_dev), "NULL argument");
+    stats_host[0] = stats_host[1] = 0.0;
+    if (n == 0) return 0;
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned long long *dev = reinterpret_cast<unsigned long long *>(ctx->hist);     // select scratch doubles as the 2-slot result
+    B2_CUDA(cudaMemsetAsync(dev, 0, 2 * sizeof(unsigned long long), st));
+    long long grid = (n + 255) / 256;
+    const long long cap = (long long)ctx->sm_count * 8;
+    if (grid > cap) grid = cap;
+    power_stats_kernel<<<(unsigned)grid, 256, 0, st>>>((const float2 *)in_dev, n, pre_scale, dev);
+    B2_CUDA(cudaGetLastError());
+    B2_CUDA(cudaMemcpyAsync(ctx->pinned, dev, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    memcpy(stats_host, ctx->pinned, 2 * sizeof(double));
+    return 0;
+}
+
+#if defined(B2_AB) && defined(B2_PIPE_TIMING)
 int b200vec_debug_pipe_prof(long long *out_host) {   // timing build only (scripts/pipe_timing.py)
     cudaDeviceSynchronize();
     return cudaMemcpyFromSymbol(out_host, b200vec::g_pipe_prof, sizeof(long long) * 320 * 16 * 8) != cudaSuccess;
@@ -580,7 +950,7 @@ int b200vec_split_planes(b200vec_ctx *ctx, const void *in_dev, int64_t n, float 
 int b200vec_box_energy(b200vec_ctx *ctx, const void *in_dev, int64_t n, int window, double *smoothed_out_dev,
                        double *max_out_dev, void *stream) {
     B2_REQUIRE(ctx && n >= 0 && (n == 0 || (in_dev && smoothed_out_dev)) && max_out_dev, "NULL argument");
-    B2_REQUIRE(window >= 1 && window <= kBoxMaxWindow, "window must be in [1, 1024]");
+    B2_REQUIRE(window >= 1 && window <= kBoxMaxWindow, "window must be in [1, 4096]");
     DeviceGuard g(ctx->device);
     cudaStream_t st = (cudaStream_t)stream;
     B2_CUDA(cudaMemsetAsync(max_out_dev, 0, sizeof(double), st));

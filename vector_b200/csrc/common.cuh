@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -29,6 +30,14 @@ inline int fail(const char *where, const char *msg) {
         }                                                                               \
     } while (0)
 
+// A/B switches (environment variables selecting measured-slower kernel variants) exist only in
+// -DB2_AB builds (make ab); the product library has one code path per op and reads no environment.
+#ifdef B2_AB
+inline const char *ab_env(const char *name) { return getenv(name); }
+#else
+inline const char *ab_env(const char *) { return nullptr; }
+#endif
+
 #define B2_REQUIRE(cond, msg)                                                           \
     do {                                                                                \
         if (!(cond)) return ::b200vec::fail(__func__, msg);                             \
@@ -50,11 +59,32 @@ struct BankSlot {
     float2 *b = nullptr;        // -> y[0] of copy B (8 mod 16)
     int64_t len = 0;            // committed length (0 = not committed)
     int64_t per = 0;            // samples per copy incl. pads; the pre-scaled copies live 2 * per after the raw ones
+    bool external = false;      // `a` is caller-owned device memory (b200vec_bank_attach): no copy B, no pads
 };
 
 struct Scratch {
     void *ptr = nullptr;
     size_t bytes = 0;
+};
+
+// State of a prepared scenario batch (b200vec_batch_prepare -> b200vec_batch_build, span.cuh)
+struct BatchState {
+    Scratch bank;               // shifted packets, one copy each, 16-byte aligned starts
+    Scratch tables;             // PlaceDesc[n_vec * pk_stride] | int np[n_vec] | ShiftJob[n_jobs] | u64 pmax[n_jobs]
+    void *pin = nullptr;        // pinned staging of the tables
+    size_t pin_bytes = 0;
+    const void *descs = nullptr;
+    const int *np = nullptr;
+    int n_vec = 0, pk_stride = 0, n_jobs = 0;
+};
+
+// Top-histogram state kept between b200vec_select_begin and b200vec_select_finish
+struct TopState {
+    std::vector<unsigned int> hist;     // host copy of the 13-bit histogram (+0 excluded)
+    unsigned long long n_poszero = 0;
+    const void *data = nullptr;
+    long long n = -1;
+    int use_abs = 0;
 };
 
 }  // namespace b200vec
@@ -68,6 +98,11 @@ struct b200vec_ctx {
     void *pinned = nullptr;               // small pinned staging block
     float2 *zeros = nullptr;              // one span of zero samples (bulk-copy source, fused1024.cuh)
     unsigned int *wf_ctr = nullptr;       // work-item counter of the warp-per-frame kernel (wf1024.cuh)
+    unsigned int *sp_ctr = nullptr;       // work-item counter / grid barrier of the span kernel (span.cuh)
+    b200vec::BatchState batch;            // prepared scenario batch
+    unsigned int *top_hist = nullptr;     // [kTopBins] u32 + one u64 (+0 count) + one u64 (candidate count)
+    b200vec::Scratch cand;                // candidate array of the fast select
+    b200vec::TopState top;
     unsigned long long *slot_max = nullptr;   // per bank slot: bits of max |y|^2 (double) of the committed packet
     int sm_count = b200vec::kSmCount;
 };

@@ -447,12 +447,12 @@ tile1024_kernel(const __grid_constant__ FArgs a) {
     if (a.flag && __syncthreads_or(anybits != 0) && tid == 0) atomicOr(a.flag, 1);
 }
 
-// W = frames per tile: 16 -> one 512-thread CTA per SM, 8 -> two 256-thread CTAs per SM.
-// B200VEC_FUSED_W=8|16 overrides the default (A/B runs, scripts/fused_ab.py).
+// W = frames per tile: 16 -> one 512-thread CTA per SM (the product path).  -DB2_AB builds also carry
+// W = 8 (two 256-thread CTAs per SM) and the bulk-tensor-store (TS / ZTMA) variants, selected by
+// B200VEC_FUSED_W / _TS / _ZTMA; all of them measured slower (profiles/r1_fused_ablation.txt).
 inline int fused_w() {
-    const char *e = getenv("B200VEC_FUSED_W");
+    const char *e = ab_env("B200VEC_FUSED_W");
     if (e && e[0] == '8') return 8;
-    if (e && e[0] == '1') return 16;
     return kFWarpsDefault;
 }
 
@@ -487,35 +487,40 @@ inline bool make_spec_tmap(CUtensorMap *tm, float *out, long long out_ld, long l
 template <bool FUSED>
 inline int launch_tile1024(b200vec_ctx *ctx, FArgs &a, long long n_frames, long long n_vec, cudaStream_t st) {
     const int w = fused_w();
-    { const char *e = getenv("B200VEC_FUSED_V"); a.dbg = e ? atoi(e) : 0; }
+    { const char *e = ab_env("B200VEC_FUSED_V"); a.dbg = e ? atoi(e) : 0; }
     const long long own = (long long)w * kFMaxHop;
     const long long t_frames = (n_frames + w - 1) / w, t_vec = (n_vec + own - 1) / own;
     a.n_tiles = t_frames > t_vec ? t_frames : t_vec;
     if (a.n_tiles == 0) return 0;
     const long long cap = (long long)ctx->sm_count * (16 / w);
     const long long grid = a.n_tiles < cap ? a.n_tiles : cap;
-    if (getenv("B200VEC_DEBUG_OCC")) {
-        int occ = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tile1024_kernel<FUSED, 8, false>, FL<8>::kThreads, FL<8>::kSmem);
-        fprintf(stderr, "[b200vec] tile1024<W=8> resident CTAs/SM: %d (smem %zu B)\n", occ, FL<8>::kSmem);
-    }
-    const char *ts_env = getenv("B200VEC_FUSED_TS");     // "1": PSD tiles leave by bulk tensor stores (measured slower: 360 vs 298 us; A/B only)
+    a.ztma = 0;
+#ifdef B2_AB
+    const char *ts_env = ab_env("B200VEC_FUSED_TS");     // "1": PSD tiles leave by bulk tensor stores (measured slower: 360 vs 298 us)
     const bool ts = ts_env && ts_env[0] == '1' && make_spec_tmap(&a.tmap, a.out, a.out_ld, n_frames, w, 256);
-    const char *z_env = getenv("B200VEC_FUSED_ZTMA");    // "1": empty tiles by bulk stores from a zeroed smem block (measured 283 vs 274 us; A/B only)
+    const char *z_env = ab_env("B200VEC_FUSED_ZTMA");    // "1": empty tiles by bulk stores from a zeroed smem block (measured 283 vs 274 us)
     a.ztma = FUSED && w == 16 && z_env && z_env[0] == '1' && make_spec_tmap(&a.tmap_z, a.out, a.out_ld, n_frames, w, 128);
     if (w == 8) {
         if (ts) tile1024_kernel<FUSED, 8, true><<<(unsigned)grid, FL<8>::kThreads, FL<8>::kSmem, st>>>(a);
         else tile1024_kernel<FUSED, 8, false><<<(unsigned)grid, FL<8>::kThreads, FL<8>::kSmem, st>>>(a);
-    } else {
-        if (ts) tile1024_kernel<FUSED, 16, true><<<(unsigned)grid, FL<16>::kThreads, FL<16>::kSmem, st>>>(a);
-        else tile1024_kernel<FUSED, 16, false><<<(unsigned)grid, FL<16>::kThreads, FL<16>::kSmem, st>>>(a);
+        B2_CUDA(cudaGetLastError());
+        return 0;
     }
+    if (ts) {
+        tile1024_kernel<FUSED, 16, true><<<(unsigned)grid, FL<16>::kThreads, FL<16>::kSmem, st>>>(a);
+        B2_CUDA(cudaGetLastError());
+        return 0;
+    }
+#endif
+    tile1024_kernel<FUSED, 16, false><<<(unsigned)grid, FL<16>::kThreads, FL<16>::kSmem, st>>>(a);
     B2_CUDA(cudaGetLastError());
     return 0;
 }
 
+#ifdef B2_AB
 bool pipe1024_enabled();                                                                   // pipe1024.cuh
 int launch_pipe1024_plain(b200vec_ctx *ctx, FArgs &a, long long n_frames, cudaStream_t st);   // pipe1024.cuh
+#endif
 
 inline int launch_tile1024_plain(b200vec_ctx *ctx, const S1Args &s, cudaStream_t st) {
     FArgs a;
@@ -524,7 +529,9 @@ inline int launch_tile1024_plain(b200vec_ctx *ctx, const S1Args &s, cudaStream_t
     a.hop = s.hop; a.in_origin = s.in_origin;
     a.window = s.window; a.tw = s.tw; a.scale = s.scale;
     a.frame_lo = s.frame_lo; a.n_frames = s.n_frames; a.out = s.out; a.out_ld = s.out_ld; a.flag = s.flag;
+#ifdef B2_AB
     if (pipe1024_enabled()) return launch_pipe1024_plain(ctx, a, s.n_frames, st);
+#endif
     return launch_tile1024<false>(ctx, a, s.n_frames, 0, st);
 }
 
@@ -538,10 +545,12 @@ inline cudaError_t fused1024_attr() {
     return cudaFuncSetAttribute(tile1024_kernel<FUSED, W, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FL<W>::kSmem);
 }
 inline int fused1024_setup() {
-    B2_CUDA((fused1024_attr<true, 16, true>()));  B2_CUDA((fused1024_attr<true, 16, false>()));
-    B2_CUDA((fused1024_attr<false, 16, true>())); B2_CUDA((fused1024_attr<false, 16, false>()));
+    B2_CUDA((fused1024_attr<true, 16, false>())); B2_CUDA((fused1024_attr<false, 16, false>()));
+#ifdef B2_AB
+    B2_CUDA((fused1024_attr<true, 16, true>()));  B2_CUDA((fused1024_attr<false, 16, true>()));
     B2_CUDA((fused1024_attr<true, 8, true>()));   B2_CUDA((fused1024_attr<true, 8, false>()));
     B2_CUDA((fused1024_attr<false, 8, true>()));  B2_CUDA((fused1024_attr<false, 8, false>()));
+#endif
     return 0;
 }
 

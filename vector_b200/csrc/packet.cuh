@@ -10,7 +10,7 @@
 namespace b200vec {
 
 constexpr int kBoxThreads = 256;
-constexpr int kBoxMaxWindow = 1024;
+constexpr int kBoxMaxWindow = 4096;             // 1 us at up to 4 GSa/s
 
 // smoothed[i] = sum_{m = i - window/2}^{i + (window-1)/2} e[m] * (1/window), e[m] = fl32(fl32(|x[m]|)^2), float64
 // accumulation in ascending m (np.convolve(energy, np.ones(w)/w, 'same'); samples outside [0, n) count 0).

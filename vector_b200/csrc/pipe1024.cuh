@@ -364,7 +364,7 @@ inline bool pipe1024_enabled() {
     // Measured on B200 (scripts/pipe_timing.py): 358 us vs 296 us for the lock-step kernel — with
     // one exchange buffer the two roles alternate on it and the 8 column warps carry the critical
     // path.  Kept as an A/B variant: B200VEC_PIPE=1 selects it.
-    const char *e = getenv("B200VEC_PIPE");
+    const char *e = ab_env("B200VEC_PIPE");
     return e && e[0] == '1';
 }
 

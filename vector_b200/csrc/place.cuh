@@ -1,4 +1,5 @@
-// place.cuh — K2/K3: output-stationary packet placement with fused max / scale.
+// place.cuh — placement descriptors shared by every builder kernel (span.cuh, wf1024.cuh, fused1024.cuh),
+// and (A/B builds only) the round-1 block-per-tile placement kernel.
 //
 // Replaces the reference's np.zeros + `vector[pos:pos+L] += y` loop + normalisation
 // (unified_gui.py:1712,1757-1769,1778-1782; main.py:218,253-257,274-277).
@@ -50,6 +51,10 @@ __device__ __forceinline__ double warp_max(double v) {
     return v;
 }
 
+#ifdef B2_AB
+// The round-1 block-per-tile placement kernel (4096-sample tiles, 16-byte loads from the two bank copies).
+// The product path is the warp-per-span kernel of span.cuh; this one stays in -DB2_AB builds as the
+// bit-exact cross-check (B200VEC_PLACE=1).
 // MODE 0: store; 1: max only; 2: scale by 1/sqrt(*maxsq) and store.
 template <int MODE>
 __global__ void __launch_bounds__(kPlaceThreads)
@@ -125,13 +130,13 @@ place_kernel(const __grid_constant__ PlaceArgs args, float2 *__restrict__ out,
 #pragma unroll
             for (int j = 0; j < kVec; ++j) {
                 const int s = 2 * (tid + kPlaceThreads * j);
-                const float q0 = (s < nvalid) ? acc[j].x * acc[j].x + acc[j].y * acc[j].y : 0.f;
-                const float q1 = (s + 1 < nvalid) ? acc[j].z * acc[j].z + acc[j].w * acc[j].w : 0.f;
-                if (q0 >= fthr) {
+                const float q0 = acc[j].x * acc[j].x + acc[j].y * acc[j].y;
+                const float q1 = acc[j].z * acc[j].z + acc[j].w * acc[j].w;
+                if (s < nvalid && q0 >= fthr) {                         // samples past the slab end never enter the max
                     const double e = (double)acc[j].x * (double)acc[j].x + (double)acc[j].y * (double)acc[j].y;
                     if (e > tmax) { tmax = e; fthr = q0 * 0.99999f; }
                 }
-                if (q1 >= fthr) {
+                if (s + 1 < nvalid && q1 >= fthr) {
                     const double e = (double)acc[j].z * (double)acc[j].z + (double)acc[j].w * (double)acc[j].w;
                     if (e > tmax) { tmax = e; fthr = q1 * 0.99999f; }
                 }
@@ -192,5 +197,6 @@ inline int launch_place(b200vec_ctx *ctx, const PlaceArgs &args, float2 *out, do
     B2_CUDA(cudaGetLastError());
     return 0;
 }
+#endif  // B2_AB
 
 }  // namespace b200vec

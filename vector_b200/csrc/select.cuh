@@ -81,7 +81,8 @@ constexpr int kSelUnroll = 4;      // 16-byte loads in flight per thread
 
 // level 1: histogram of the top 11 key bits over all selected elements
 __global__ void __launch_bounds__(kSelThreads)
-sel_hist1(const float *__restrict__ x, long long n, int positive_only, unsigned int *__restrict__ hist) {
+sel_hist1(const float *__restrict__ x, long long n, int flags, unsigned int *__restrict__ hist) {
+    const bool positive_only = flags & 1, use_abs = flags & 2;
     __shared__ unsigned int h[kBins1];
     for (int i = threadIdx.x; i < kBins1; i += kSelThreads) h[i] = 0;
     __syncthreads();
@@ -99,7 +100,10 @@ sel_hist1(const float *__restrict__ x, long long n, int positive_only, unsigned 
         for (int u = 0; u < kSelUnroll; ++u)
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-                warp_hist_add(h, f2key(v[u][k]) >> 21, in[u][k] && (positive_only ? v[u][k] > 0.f : true));
+            {
+                const float val = use_abs ? fabsf(v[u][k]) : v[u][k];
+                warp_hist_add(h, f2key(val) >> 21, in[u][k] && (positive_only ? val > 0.f : true));
+            }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < kBins1; i += kSelThreads)
@@ -111,7 +115,8 @@ sel_hist1(const float *__restrict__ x, long long n, int positive_only, unsigned 
 // common case (none) costs one shared load per element.
 template <int LEVEL>
 __global__ void __launch_bounds__(kSelThreads)
-sel_histN(const float *__restrict__ x, long long n, int positive_only, unsigned int *__restrict__ hist) {
+sel_histN(const float *__restrict__ x, long long n, int flags, unsigned int *__restrict__ hist) {
+    const bool positive_only = flags & 1, use_abs = flags & 2;
     constexpr int BINS = (LEVEL == 2) ? kBins2 : kBins3;
     constexpr int SHIFT_PREFIX = (LEVEL == 2) ? 21 : 10;
     extern __shared__ unsigned int hs[];          // [n_ranks][BINS]
@@ -152,8 +157,9 @@ sel_histN(const float *__restrict__ x, long long n, int positive_only, unsigned 
         for (int u = 0; u < kSelUnroll; ++u) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const bool ok = in[u][k] && (positive_only ? v[u][k] > 0.f : true);
-                const unsigned int key = f2key(v[u][k]);
+                const float val = use_abs ? fabsf(v[u][k]) : v[u][k];
+                const bool ok = in[u][k] && (positive_only ? val > 0.f : true);
+                const unsigned int key = f2key(val);
                 unsigned int mine = ok ? lut[key >> 21] : 0u;        // candidate histograms of this element
                 if (!__any_sync(0xffffffffu, mine != 0)) continue;   // most elements match no prefix
                 const unsigned int top = key >> SHIFT_PREFIX;
@@ -244,6 +250,106 @@ sel_pick(unsigned int *__restrict__ hist) {
         }
         __syncthreads();
     }
+}
+
+// ---------------------------------------------------------------------------------------
+// Fast path of the order statistics: ONE full read for a 13-bit top histogram (+ the exact count of +0,
+// the one value real spectrograms repeat by the tens of millions — it never touches an atomic), the host
+// picks the bin of every rank, ONE more full read compacts the few elements of those bins into a candidate
+// array, and the exact 3-level select above runs on the candidates only.  Falls back to the 3-level select
+// on the whole array when the bins in question hold too many elements (a heavily repeated non-zero value).
+constexpr int kTopBits = 13;
+constexpr int kTopBins = 1 << kTopBits;                // sign + 8 exponent bits + 4 mantissa bits: 0.19 dB per bin
+constexpr int kTopShift = 32 - kTopBits;
+constexpr unsigned int kTopZeroBin = 0x80000000u >> kTopShift;      // first bin of the non-negative keys
+
+__global__ void __launch_bounds__(kSelThreads)
+sel_top_kernel(const float *__restrict__ x, long long n, int use_abs, unsigned int *__restrict__ hist,
+               unsigned long long *__restrict__ n_poszero) {
+    __shared__ unsigned int h[kTopBins];
+    for (int i = threadIdx.x; i < kTopBins; i += kSelThreads) h[i] = 0;
+    __syncthreads();
+    const bool aligned = (reinterpret_cast<unsigned long long>(x) & 15ull) == 0;
+    const long long groups = (n + 3) / 4;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    unsigned int zc = 0;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += stride * kSelUnroll) {
+        float v[kSelUnroll][4]; bool in[kSelUnroll][4];
+#pragma unroll
+        for (int u = 0; u < kSelUnroll; ++u) {
+            const long long gg = g + u * stride;
+            if (gg < groups) sel_load4(x, n, gg, aligned, v[u], in[u]);
+            else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { v[u][k] = 0.f; in[u][k] = false; }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kSelUnroll; ++u)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (!in[u][k]) continue;
+                const float val = use_abs ? fabsf(v[u][k]) : v[u][k];
+                if (__float_as_uint(val) == 0u) ++zc;
+                else atomicAdd(&h[f2key(val) >> kTopShift], 1u);
+            }
+    }
+    zc = __reduce_add_sync(0xffffffffu, zc);
+    if ((threadIdx.x & 31) == 0 && zc) atomicAdd(n_poszero, (unsigned long long)zc);
+    __syncthreads();
+    for (int i = threadIdx.x; i < kTopBins; i += kSelThreads)
+        if (h[i]) atomicAdd(&hist[i], h[i]);
+}
+
+struct SelBins {
+    unsigned int bin[B200VEC_MAX_RANKS];
+    int n;
+};
+
+// cand[...] <- every element (after the optional abs) whose top bits name one of `sel`'s bins, +0 excluded
+__global__ void __launch_bounds__(kSelThreads)
+sel_compact_kernel(const float *__restrict__ x, long long n, int use_abs, const SelBins sel,
+                   float *__restrict__ cand, unsigned long long cap, unsigned long long *__restrict__ count) {
+    const bool aligned = (reinterpret_cast<unsigned long long>(x) & 15ull) == 0;
+    const long long groups = (n + 3) / 4;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long g0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long step = stride * kSelUnroll;
+    const long long g_round = ((groups + step - 1) / step) * step;           // keep warps converged for the ballots
+    const int lane = threadIdx.x & 31;
+    for (long long g = g0; g < g_round; g += step) {
+        float v[kSelUnroll][4]; bool in[kSelUnroll][4];
+#pragma unroll
+        for (int u = 0; u < kSelUnroll; ++u) sel_load4(x, n, g + u * stride, aligned, v[u], in[u]);
+#pragma unroll
+        for (int u = 0; u < kSelUnroll; ++u)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float val = use_abs ? fabsf(v[u][k]) : v[u][k];
+                const unsigned int b = f2key(val) >> kTopShift;
+                bool hit = false;
+#pragma unroll
+                for (int r = 0; r < B200VEC_MAX_RANKS; ++r) hit |= (r < sel.n && b == sel.bin[r]);
+                hit = hit && in[u][k] && __float_as_uint(val) != 0u;
+                const unsigned int m = __ballot_sync(0xffffffffu, hit);
+                if (m == 0) continue;
+                unsigned long long base = 0;
+                if (lane == __ffs(m) - 1) base = atomicAdd(count, (unsigned long long)__popc(m));
+                base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+                const unsigned long long pos = base + __popc(m & ((1u << lane) - 1u));
+                if (hit && pos < cap) cand[pos] = val;
+            }
+    }
+}
+
+// out[i] = in[i * stride]: the naive decimation of create_spectrogram (utils.py:192-195, sig[::factor])
+// made once, so that the overlapping preview frames re-read a compact, L2-resident copy instead of one
+// 32-byte sector per sample and frame.
+__global__ void __launch_bounds__(256)
+decimate_kernel(const float2 *__restrict__ in, long long n_out, long long stride, float2 *__restrict__ out) {
+    const long long st = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_out; i += st)
+        out[i] = __ldcs(in + i * stride);
 }
 
 }  // namespace b200vec

@@ -1,0 +1,357 @@
+// span.cuh — K2/K3 (and the cfg5 batch form): output-stationary packet placement with fused max / scale,
+// one WARP per 512-sample span — the structure of the fused step's builder (wf1024.cuh) without the
+// transforms, for one vector or for a batch of independent vectors.
+//
+// Replaces the reference's np.zeros + `vector[pos:pos+L] += y` loop + normalisation
+// (unified_gui.py:1712,1757-1769,1778-1782; main.py:218,253-257,274-277), per vector; a batch is the
+// scenario sweep that runs that method once per scenario (BASELINE.json configs[4]).
+//
+// Work item = kSpChunk consecutive halves (512 samples each) of one vector, handed out by a global
+// counter.  Per item a warp
+//   S  finds, per packet (lane p), the instance range overlapping the item (two 64-bit floor divisions);
+//   B  per half: lane l owns x[l + 32 j]; for every overlapping (packet, instance) in the reference's
+//      order it adds the packet samples (8-byte loads, 256 B per warp instruction, from the L2-resident
+//      bank), scales by fl32(1 / fl32(sqrt(max |v|^2))) and sends the 4 KB half to HBM as ONE bulk copy
+//      (cp.async.bulk shared -> global) out of the warp's staging block; halves nothing overlaps leave
+//      from a block of zeros.  Every output sample is written exactly once; no atomics on data.
+// Normalisation: MAXONLY reduces max |v|^2 (exact fp64 products) per vector with no stores; SCALE reads
+// it; NORM does both in one cooperative launch (max pass, grid barrier, scale pass) — per vector, so a
+// batch of 256 scenario vectors is ONE launch.  HBM traffic: 8 B per output sample, nothing read.
+#pragma once
+#include "common.cuh"
+#include "place.cuh"
+#include "wf1024.cuh"        // bank-load / bulk-store helpers shared with the fused step
+
+namespace b200vec {
+
+constexpr int kSpWarps = 8;
+constexpr int kSpThreads = 32 * kSpWarps;
+constexpr int kSpChunk = 4;                                       // halves per work item
+constexpr int kSpNorm = 3;                                        // SpanArgs::mode: max pass + grid barrier + scale pass
+constexpr size_t kSpSmem = (size_t)kSpWarps * 4096 + 4096;        // per-warp staging blocks + one block of zeros
+
+struct SpanArgs {
+    PlaceArgs place;             // single vector: descriptors by value (constant bank); place.lo/hi unused
+    const PlaceDesc *gdesc;      // batch: [n_vec][pk_stride] descriptors in device memory (NULL: single vector)
+    const int *gnp;              // batch: packets per vector
+    int n_vec, pk_stride;
+    long long lo, hi;            // every vector: samples [lo, hi) are built
+    float2 *out;                 // vector v at out + v * out_ld; element 0 = sample lo
+    long long out_ld;
+    unsigned long long *maxsq;   // [n_vec] bits of max |v|^2 (double): MAXONLY / NORM raise it, SCALE / NORM read it
+    int mode;                    // B200VEC_BUILD_STORE | _MAXONLY | _SCALE | kSpNorm
+    long long norm_lo[kWfMaxNormRanges], norm_hi[kWfMaxNormRanges];   // MAXONLY / NORM: ranges evaluated (every vector)
+    int n_norm;
+    long long norm_units;        // 1024-sample units per vector over all ranges
+    unsigned int *ctr;           // [0] next work item, [2] grid barrier; zeroed on the stream before every launch
+};
+
+template <bool BATCH>
+__device__ __forceinline__ const PlaceDesc &sp_desc(const SpanArgs &a, const PlaceDesc *dv, int p) {
+    if constexpr (BATCH) return dv[p];
+    else return a.place.d[p];
+}
+
+// S: instances of packet `lane` overlapping [s0, s0 + span)
+template <bool BATCH>
+__device__ __forceinline__ void sp_overlap(const SpanArgs &a, const PlaceDesc *dv, int np, int lane, long long s0,
+                                           int span, int &cnt_l, int &rel0_l) {
+    cnt_l = 0; rel0_l = 0;
+    if (lane < np) {
+        const PlaceDesc &d = sp_desc<BATCH>(a, dv, lane);
+        const long long start = d.start, period = d.period, count = d.count;
+        const int len = d.len;
+        long long klo = floor_div(s0 - len - start, period) + 1;
+        long long khi = floor_div(s0 + span - 1 - start, period);
+        if (klo < 0) klo = 0;
+        if (khi > count - 1) khi = count - 1;
+        const long long cn = khi - klo + 1;
+        cnt_l = cn > 0 ? (int)(cn < 0x00ffffff ? cn : 0x00ffffff) : 0;
+        rel0_l = cnt_l ? (int)(s0 - (start + klo * period)) : 0;
+    }
+}
+
+// Pass A only: the 512 samples at `off` lie inside exactly ONE instance of a packet whose whole-packet
+// max is attained elsewhere in the vector (PlaceDesc::free_inst) -> nothing to read (wf_norm_can_skip).
+template <bool BATCH>
+__device__ __forceinline__ bool sp_can_skip(const SpanArgs &a, const PlaceDesc *dv, unsigned active, int cnt_l,
+                                            int rel0_l, int off) {
+    int n_ov = 0;
+    bool ok = false;
+    for (unsigned m = active; m; m &= m - 1) {
+        const int p = __ffs(m) - 1;
+        const int cnt = __shfl_sync(0xffffffffu, cnt_l, p);
+        const int rel0 = __shfl_sync(0xffffffffu, rel0_l, p);
+        const PlaceDesc &d = sp_desc<BATCH>(a, dv, p);
+        const int len = d.len;
+        const long long period = d.period;
+        const bool fr = d.free_inst != 0;
+        long long r64 = (long long)rel0 + off;
+        for (int i = 0; i < cnt; ++i, r64 -= period) {
+            if (r64 + 512 <= 0) break;
+            if (r64 >= len) continue;
+            ++n_ov;
+            ok = fr && r64 >= 0 && r64 + 512 <= len;
+        }
+    }
+    return n_ov == 1 && ok;
+}
+
+// B: the 512 samples starting `off` samples into the item; false when nothing overlaps them (x == 0).
+template <bool BATCH>
+__device__ __forceinline__ bool sp_build_half(const SpanArgs &a, const PlaceDesc *dv, unsigned active, int cnt_l,
+                                              int rel0_l, int off, int lane, float2 (&x)[16], unsigned long long keep) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] = make_float2(0.f, 0.f);
+    bool live = false;
+    for (unsigned m = active; m; m &= m - 1) {
+        const int p = __ffs(m) - 1;
+        const int cnt = __shfl_sync(0xffffffffu, cnt_l, p);
+        const int rel0 = __shfl_sync(0xffffffffu, rel0_l, p);
+        const PlaceDesc &d = sp_desc<BATCH>(a, dv, p);
+        const int len = d.len;
+        const long long period = d.period;
+        const float2 *ya = d.a;
+        long long r64 = (long long)rel0 + off;               // packet index of the half's sample 0 for instance klo + i
+        for (int i = 0; i < cnt; ++i, r64 -= period) {
+            if (r64 + 512 <= 0) break;                       // this and every later instance start after the half
+            if (r64 >= len) continue;                        // instance ended before the half
+            const int r = (int)r64;
+            live = true;
+            const float2 *base = ya + r + lane;
+            if (r >= 0 && r + 512 <= len) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float2 v = wf_ldg_keep(base + 32 * j, keep);
+                    x[j].x += v.x; x[j].y += v.y;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const int n = r + lane + 32 * j;
+                    if (n >= 0 && n < len) {
+                        const float2 v = wf_ldg_keep(base + 32 * j, keep);
+                        x[j].x += v.x; x[j].y += v.y;
+                    }
+                }
+            }
+        }
+    }
+    return live;
+}
+
+template <bool BATCH>
+__global__ void __launch_bounds__(kSpThreads)
+span_kernel(const __grid_constant__ SpanArgs a) {
+    extern __shared__ __align__(16) unsigned char sp_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float2 *vst = reinterpret_cast<float2 *>(sp_smem) + warp * 512;
+    const unsigned zero_u32 = smem_u32(sp_smem + (size_t)kSpWarps * 4096);
+    for (int i = tid; i < 256; i += kSpThreads)
+        reinterpret_cast<float4 *>(sp_smem + (size_t)kSpWarps * 4096)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    wf_fence_async();
+    __syncthreads();
+    const unsigned long long keep = wf_policy_evict_last();
+    const unsigned long long pol = wf_policy_evict_first();
+    const long long gw = (long long)blockIdx.x * kSpWarps + warp, nw = (long long)gridDim.x * kSpWarps;
+
+    if (a.mode == B200VEC_BUILD_MAXONLY || a.mode == kSpNorm) {
+        // ---------------------------------------------------------------- pass A: max |v|^2 per vector, no stores
+        const long long total_units = a.norm_units * a.n_vec;
+        double tmax = 0.0;                                   // running max of |v|^2 for vector cur_v (exact products in fp64)
+        float fthr = 0.0f;                                   // fp32 pre-filter threshold
+        int cur_v = -1;
+        for (long long u = gw; u < total_units; u += nw) {
+            const int v = BATCH ? (int)(u / a.norm_units) : 0;
+            long long w = BATCH ? u - (long long)v * a.norm_units : u;
+            if (v != cur_v) {
+                if (cur_v >= 0) {
+                    tmax = warp_max(tmax);
+                    if (lane == 0 && tmax > 0.0) atomicMax(a.maxsq + cur_v, (unsigned long long)__double_as_longlong(tmax));
+                }
+                cur_v = v; tmax = 0.0; fthr = 0.0f;
+            }
+            long long s0 = 0, s1 = 0;
+            for (int r = 0; r < a.n_norm; ++r) {
+                const long long nu = (a.norm_hi[r] - a.norm_lo[r] + 1023) / 1024;
+                if (w < nu) { s0 = a.norm_lo[r] + w * 1024; s1 = a.norm_hi[r]; break; }
+                w -= nu;
+            }
+            if (s1 > s0 + 1024) s1 = s0 + 1024;
+            const PlaceDesc *dv = BATCH ? a.gdesc + (long long)v * a.pk_stride : nullptr;
+            const int np = BATCH ? a.gnp[v] : a.place.np;
+            int cnt_l, rel0_l;
+            sp_overlap<BATCH>(a, dv, np, lane, s0, 1024, cnt_l, rel0_l);
+            const unsigned active = __ballot_sync(0xffffffffu, cnt_l > 0);
+            if (!active) continue;
+            for (int half = 0; half < 2; ++half) {
+                const int valid = (int)(s1 - s0) - 512 * half;
+                if (valid <= 0) break;
+                float2 x[16];
+                if (sp_can_skip<BATCH>(a, dv, active, cnt_l, rel0_l, 512 * half)) continue;
+                if (!sp_build_half<BATCH>(a, dv, active, cnt_l, rel0_l, 512 * half, lane, x, keep)) continue;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float q = x[j].x * x[j].x + x[j].y * x[j].y;
+                    if (lane + 32 * j < valid && q >= fthr) {          // samples past the range end never enter the max
+                        const double e = (double)x[j].x * (double)x[j].x + (double)x[j].y * (double)x[j].y;
+                        if (e > tmax) { tmax = e; fthr = q * 0.99999f; }
+                    }
+                }
+            }
+        }
+        if (cur_v >= 0) {
+            tmax = warp_max(tmax);
+            if (lane == 0 && tmax > 0.0) atomicMax(a.maxsq + cur_v, (unsigned long long)__double_as_longlong(tmax));
+        }
+        for (long long v = gw; v < a.n_vec; v += nw) {       // whole-packet maxima the skipped spans stand for
+            const PlaceDesc *dv = BATCH ? a.gdesc + v * a.pk_stride : nullptr;
+            const int np = BATCH ? a.gnp[v] : a.place.np;
+            if (lane < np) {
+                const PlaceDesc &d = sp_desc<BATCH>(a, dv, lane);
+                if (d.free_inst && d.count > 0) {
+                    const unsigned long long pm = *d.pmax;
+                    if (pm) atomicMax(a.maxsq + v, pm);
+                }
+            }
+        }
+        if (a.mode == B200VEC_BUILD_MAXONLY) return;
+        __syncthreads();
+        if (tid == 0) {                                      // grid barrier (cooperative launch: every CTA is resident)
+            __threadfence();
+            atomicAdd(a.ctr + 2, 1u);
+            while (*reinterpret_cast<volatile unsigned int *>(a.ctr + 2) < gridDim.x) __nanosleep(40);
+            __threadfence();
+        }
+        __syncthreads();
+    }
+
+    // -------------------------------------------------------------------- pass B: place, scale, store
+    const long long n = a.hi - a.lo;
+    const long long halves = (n + 511) / 512;
+    const long long ipv = (halves + kSpChunk - 1) / kSpChunk;                 // items per vector
+    const long long n_items = ipv * a.n_vec;
+    const bool scaled = a.mode == B200VEC_BUILD_SCALE || a.mode == kSpNorm;
+    unsigned next = 0;
+    if (lane == 0) next = atomicAdd(a.ctr, 1u);
+    for (;;) {
+        const long long c = __shfl_sync(0xffffffffu, next, 0);
+        if (c >= n_items) break;
+        if (lane == 0) next = atomicAdd(a.ctr, 1u);         // the next item's index arrives while this one is processed
+        const int v = BATCH ? (int)(c / ipv) : 0;
+        const long long h0 = (BATCH ? c - (long long)v * ipv : c) * kSpChunk;     // first half of the item
+        const int nh = (int)(halves - h0 < kSpChunk ? halves - h0 : kSpChunk);
+        float scl = 1.0f;
+        if (scaled) {
+            const double m2 = __longlong_as_double((long long)__ldcg(a.maxsq + v));
+            if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);     // numpy's complex64 / float32: multiply by the fp32 reciprocal
+        }
+        const PlaceDesc *dv = BATCH ? a.gdesc + (long long)v * a.pk_stride : nullptr;
+        const int np = BATCH ? a.gnp[v] : a.place.np;
+        int cnt_l, rel0_l;
+        sp_overlap<BATCH>(a, dv, np, lane, a.lo + h0 * 512, nh * 512, cnt_l, rel0_l);
+        const unsigned active = __ballot_sync(0xffffffffu, cnt_l > 0);
+        float2 *dst = a.out + (long long)v * a.out_ld;
+#pragma unroll 1
+        for (int h = 0; h < nh; ++h) {
+            float2 x[16];
+            const bool live = active && sp_build_half<BATCH>(a, dv, active, cnt_l, rel0_l, h * 512, lane, x, keep);
+            if (!live) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) x[j] = make_float2(0.f, 0.f);
+            }
+            wf_store_half<true, true>(dst, (h0 + h) * 512, n, live, scl, lane, x, vst, zero_u32, pol);
+        }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+inline int span_setup() {
+    B2_CUDA(cudaFuncSetAttribute(span_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmem));
+    B2_CUDA(cudaFuncSetAttribute(span_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmem));
+    B2_CUDA(cudaFuncSetAttribute(span_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+    B2_CUDA(cudaFuncSetAttribute(span_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+    return 0;
+}
+
+// a.place (or gdesc/gnp), n_vec, lo/hi, out, maxsq, mode and the norm ranges are filled by the caller.
+inline int launch_span(b200vec_ctx *ctx, SpanArgs &a, cudaStream_t st) {
+    const long long n = a.hi - a.lo;
+    if (a.n_vec <= 0) return 0;
+    const bool batch = a.gdesc != nullptr;
+    const bool pass_a = a.mode == B200VEC_BUILD_MAXONLY || a.mode == kSpNorm;
+    const bool pass_b = a.mode != B200VEC_BUILD_MAXONLY;
+    a.norm_units = 0;
+    if (pass_a)
+        for (int r = 0; r < a.n_norm; ++r) a.norm_units += (a.norm_hi[r] - a.norm_lo[r] + 1023) / 1024;
+    if ((!pass_b || n <= 0) && a.norm_units == 0) return 0;
+    B2_REQUIRE(!pass_b || n <= 0 || (((uintptr_t)a.out & 15) == 0 && (a.n_vec == 1 || (a.out_ld & 1) == 0)),
+               "output must be 16-byte aligned (and the vector pitch even)");
+    if (!ctx->sp_ctr) B2_CUDA(cudaMalloc(&ctx->sp_ctr, 4 * sizeof(unsigned int)));
+    B2_CUDA(cudaMemsetAsync(ctx->sp_ctr, 0, 4 * sizeof(unsigned int), st));
+    a.ctr = ctx->sp_ctr;
+    static int occ[2] = {0, 0};            // resident CTAs per SM (register / shared-memory limited)
+    if (!occ[batch]) {
+        if (batch) B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1], span_kernel<true>, kSpThreads, kSpSmem));
+        else B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0], span_kernel<false>, kSpThreads, kSpSmem));
+        B2_REQUIRE(occ[batch] > 0, "span_kernel does not fit an SM");
+    }
+    const long long halves = n > 0 ? (n + 511) / 512 : 0;
+    const long long items = pass_b ? (halves + kSpChunk - 1) / kSpChunk * a.n_vec : 0;
+    const long long units = a.norm_units * a.n_vec;
+    const long long work = items > units ? items : units;
+    const long long cap = (long long)ctx->sm_count * occ[batch];       // one full wave: persistent warps, dynamic items
+    long long grid = (work + kSpWarps - 1) / kSpWarps;
+    if (grid > cap) grid = cap;
+    if (grid < 1) grid = 1;
+    B2_REQUIRE(items < 0x7fffffffLL - cap * kSpWarps, "too many work items for one launch (split the batch)");
+    void *kargs[] = {&a};
+    if (a.mode == kSpNorm) {               // grid barrier between the passes: cooperative launch
+        if (batch) B2_CUDA(cudaLaunchCooperativeKernel((const void *)span_kernel<true>, dim3((unsigned)grid), dim3(kSpThreads), kargs, kSpSmem, st));
+        else B2_CUDA(cudaLaunchCooperativeKernel((const void *)span_kernel<false>, dim3((unsigned)grid), dim3(kSpThreads), kargs, kSpSmem, st));
+    } else if (batch) {
+        span_kernel<true><<<(unsigned)grid, kSpThreads, kSpSmem, st>>>(a);
+    } else {
+        span_kernel<false><<<(unsigned)grid, kSpThreads, kSpSmem, st>>>(a);
+    }
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// Batch bank: every distinct (source packet, frequency shift) of a scenario sweep shifted in ONE launch
+// (apply_frequency_shift, utils.py:120-127 — the arithmetic of shift_commit_kernel), plus max |y|^2 of
+// each shifted packet for the pass-A hint.
+struct ShiftJob {
+    const float2 *src;           // committed or uploaded source samples
+    float2 *dst;                 // len samples in the batch bank (8-byte loads only: one copy)
+    unsigned long long *pmax;    // bits of max |y|^2 (double), zeroed by the caller
+    long long len;
+    double w;                    // (2*pi)*f, formed on the host in the reference's order
+    int do_shift;
+};
+
+__global__ void __launch_bounds__(256)
+batch_shift_kernel(const ShiftJob *__restrict__ jobs, double fs) {
+    const ShiftJob jb = jobs[blockIdx.y];
+    double m = 0.0;
+    for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < jb.len; n += (long long)gridDim.x * blockDim.x) {
+        float2 y = jb.src[n];
+        if (jb.do_shift) {
+            const double t = (double)n / fs;
+            const double ph = __dmul_rn(jb.w, t);
+            double s, c;
+            sincos(ph, &s, &c);
+            const double xr = (double)y.x, xi = (double)y.y;
+            const double re = __dsub_rn(__dmul_rn(xr, c), __dmul_rn(xi, s));
+            const double im = __dadd_rn(__dmul_rn(xr, s), __dmul_rn(xi, c));
+            y = make_float2((float)re, (float)im);
+        }
+        jb.dst[n] = y;
+        m = fmax(m, (double)y.x * (double)y.x + (double)y.y * (double)y.y);
+    }
+    m = warp_max(m);
+    if ((threadIdx.x & 31) == 0 && m > 0.0) atomicMax(jb.pmax, (unsigned long long)__double_as_longlong(m));
+}
+
+}  // namespace b200vec

@@ -334,12 +334,14 @@ stft1024_tma_kernel(const S1Args a) {
 inline int stft1024_setup() {
     B2_CUDA(cudaFuncSetAttribute(stft1024_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kS1Smem));
     B2_CUDA(cudaFuncSetAttribute(stft1024_tma_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T1<16>::kSmem));
+#ifdef B2_AB
     B2_CUDA(cudaFuncSetAttribute(stft1024_tma_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T1<8>::kSmem));
+#endif
     return 0;
 }
 
 inline bool stft1024_enabled() {
-    const char *e = getenv("B200VEC_STFT1024");            // "0" forces the generic kernel (A/B tests)
+    const char *e = ab_env("B200VEC_STFT1024");            // "0" forces the generic kernel (A/B builds)
     return !(e && e[0] == '0');
 }
 
@@ -374,23 +376,27 @@ inline int launch_stft1024(b200vec_ctx *ctx, const float2 *in, long long in_orig
     a.out = out; a.out_ld = out_ld; a.flag = flag;
     if (get_tw1024(ctx, &a.tw)) return 1;
     const long long n_tiles = (n_frames + kS1Frames - 1) / kS1Frames;
-    const char *no_tma = getenv("B200VEC_STFT_TMA");          // "0" forces the gather kernel (A/B tests)
+    const char *no_tma = ab_env("B200VEC_STFT_TMA");          // "0" forces the gather kernel (A/B builds)
     const long long first = frame_lo * (long long)hop - in_origin;
     const bool tma_ok = stride == 1 && nperseg == 1024 && hop <= 512 && (hop & 1) == 0 &&
                         ((reinterpret_cast<uintptr_t>(in + first)) & 15) == 0 && !(no_tma && no_tma[0] == '0');
     if (tma_ok) {
-        const char *wsel = getenv("B200VEC_STFT_W");           // "8"/"16": the v2 tile-transposing kernels (A/B tests)
-        if (!wsel && out_ld < (1LL << 24)) {                   // default: direct-store kernel (fused1024.cuh)
+        const char *wsel = ab_env("B200VEC_STFT_W");           // "8"/"16": the v2 tile-transposing kernels (A/B builds)
+        if (!wsel && out_ld < (1LL << 24))                     // default: direct-store kernel (fused1024.cuh)
             return launch_tile1024_plain(ctx, a, st);
-        } else if (wsel[0] == '8') {
+#ifdef B2_AB
+        if (wsel && wsel[0] == '8') {
             const long long nt = (n_frames + 7) / 8;
             long long grid = nt < 2LL * ctx->sm_count ? nt : 2LL * ctx->sm_count;
             stft1024_tma_kernel<8><<<(unsigned)grid, 256, T1<8>::kSmem, st>>>(a);
-        } else {                                               // measured on B200: 277 us vs 293 us at 56 M samples
-            const long long nt = (n_frames + 15) / 16;
-            long long grid = nt < ctx->sm_count ? nt : ctx->sm_count;
-            stft1024_tma_kernel<16><<<(unsigned)grid, 512, T1<16>::kSmem, st>>>(a);
+            B2_CUDA(cudaGetLastError());
+            return 0;
         }
+#endif
+        // rows longer than 2^24 frames (the direct-store kernel's 32-bit row offsets end there): tile-transposing kernel
+        const long long nt = (n_frames + 15) / 16;
+        long long grid = nt < ctx->sm_count ? nt : ctx->sm_count;
+        stft1024_tma_kernel<16><<<(unsigned)grid, 512, T1<16>::kSmem, st>>>(a);
     } else {
         long long grid = n_tiles < 2LL * ctx->sm_count ? n_tiles : 2LL * ctx->sm_count;
         stft1024_gather_kernel<<<(unsigned)grid, kS1Threads, kS1Smem, st>>>(a);

@@ -57,6 +57,7 @@ constexpr int kWfMaxNormRanges = 4;
 constexpr int kWfAutoNorm = 3;                                    // WfArgs::mode: find the max in-kernel, then scale
 constexpr int kWfAutoNormPeer = 4;                                // same, and MAX-combine it with the other GPUs through peer memory
 constexpr int kWfMaxPeers = 8;
+constexpr long long kWfPeerTimeoutClocks = 4000000000LL;          // ~2 s at 1.9 GHz: bound of the in-kernel wait for the other GPUs
 constexpr int kWfExPitch = 33;                                    // float2 per l-row of a warp's exchange block
 constexpr size_t kWfOffExch = 0;
 constexpr size_t kWfOffTw = kWfOffExch + (size_t)kWfWarps * 32 * kWfExPitch * sizeof(float2);
@@ -93,7 +94,10 @@ struct WfArgs {
     int world, rank;
     unsigned int epoch;          // 1, 2, 3, ... identical on every rank for the same step; 0: count steps on the device
                                  // (u32 at byte 24 of the home block), which lets a step be replayed from a CUDA graph
-    unsigned int *ctr;           // [0] next work item, [1] finished CTAs, [2] grid barrier, [4..5] max |v|^2 bits (all zero between launches); [3] epoch published, [6..7] combined max (peer mode)
+    unsigned int *ctr;           // per-launch words, zeroed on the stream before every launch (and re-armed by the last CTA):
+                                 //   [0] next work item, [1] finished CTAs, [2] grid barrier, [4..5] max |v|^2 bits
+                                 // persistent words (peer mode): [6] epoch published, [8..9] combined max,
+                                 //   [10] sticky error flag: 1 = the peer exchange timed out (b200vec_peer_status)
 };
 
 // Packet-bank loads ask L2 to keep their lines (evict_last) and the output leaves with evict_first, so the
@@ -326,8 +330,8 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                 if (!wf_build_half(a, active, cnt_l, rel0_l, 512 * half, lane, x, keep)) continue;
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
-                    const float q = (lane + 32 * j < valid) ? x[j].x * x[j].x + x[j].y * x[j].y : 0.f;
-                    if (q >= fthr) {
+                    const float q = x[j].x * x[j].x + x[j].y * x[j].y;
+                    if (lane + 32 * j < valid && q >= fthr) {      // samples past the range end never enter the max
                         const double e = (double)x[j].x * (double)x[j].x + (double)x[j].y * (double)x[j].y;
                         if (e > tmax) { tmax = e; fthr = q * 0.99999f; }
                     }
@@ -354,29 +358,46 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
             // waits for all `world` arrivals at home; the other CTAs wait for the combined value it publishes.
             // Slots alternate with the epoch's parity; a slot is cleared one epoch before it is used again,
             // ahead of the arrival signal that lets any peer start that epoch.
-            unsigned long long *fin = reinterpret_cast<unsigned long long *>(a.ctr + 6);
+            unsigned long long *fin = reinterpret_cast<unsigned long long *>(a.ctr + 8);
             unsigned long long *home = a.peer[a.rank];
             const unsigned int epoch = a.epoch ? a.epoch : *reinterpret_cast<volatile unsigned int *>(home + 3) + 1u;
-            if (blockIdx.x == 0 && tid == 0) {
+            if (blockIdx.x == 0 && warp == 0) {
+                // lane r talks to GPU r: the `world` remote updates travel over NVLink side by side
                 const unsigned long long mine = *reinterpret_cast<volatile unsigned long long *>(slot);
                 const int cur = epoch & 1;
-                home[cur ^ 1] = 0ull;
+                if (lane == 0) home[cur ^ 1] = 0ull;
                 __threadfence_system();
-                for (int r = 0; r < a.world; ++r)
-                    if (mine) atomicMax_system(a.peer[r] + cur, mine);
-                __threadfence_system();
-                for (int r = 0; r < a.world; ++r)
-                    atomicAdd_system(reinterpret_cast<unsigned int *>(a.peer[r] + 2), 1u);
-                volatile unsigned int *arr = reinterpret_cast<volatile unsigned int *>(home + 2);
-                const unsigned int want = epoch * (unsigned)a.world;
-                while ((int)(*arr - want) < 0) __nanosleep(100);
-                __threadfence_system();
-                *fin = *reinterpret_cast<volatile unsigned long long *>(home + cur);
-                __threadfence();
-                atomicExch(a.ctr + 3, epoch);
+                if (lane < a.world) {
+                    if (mine) atomicMax_system(a.peer[lane] + cur, mine);
+                    __threadfence_system();                  // the max lands before the arrival that announces it
+                    atomicAdd_system(reinterpret_cast<unsigned int *>(a.peer[lane] + 2), 1u);
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    // home is local memory: poll it back to back.  The wait is bounded (a rank that never launched
+                    // must not hang the other GPUs): on a timeout the step goes on with the local max and the
+                    // sticky error flag tells the host (b200vec_peer_status).
+                    volatile unsigned int *arr = reinterpret_cast<volatile unsigned int *>(home + 2);
+                    const unsigned int want = epoch * (unsigned)a.world;
+                    const long long t0 = clock64();
+                    bool ok = true;
+                    while ((int)(*arr - want) < 0) {
+                        if (clock64() - t0 > kWfPeerTimeoutClocks) { ok = false; break; }
+                    }
+                    __threadfence_system();
+                    unsigned long long all = *reinterpret_cast<volatile unsigned long long *>(home + cur);
+                    if (!ok) { a.ctr[10] = 1u; if (mine > all) all = mine; }
+                    *fin = all;
+                    __threadfence();
+                    atomicExch(a.ctr + 6, epoch);
+                }
             }
             if (tid == 0) {
-                while (*reinterpret_cast<volatile unsigned int *>(a.ctr + 3) != epoch) __nanosleep(40);
+                const long long t0 = clock64();
+                while (*reinterpret_cast<volatile unsigned int *>(a.ctr + 6) != epoch) {
+                    __nanosleep(20);
+                    if (clock64() - t0 > 2 * kWfPeerTimeoutClocks) break;      // CTA 0 has flagged the error by then
+                }
                 __threadfence();
             }
             __syncthreads();
@@ -548,7 +569,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         if (done == gridDim.x - 1) {
             a.ctr[0] = 0; a.ctr[1] = 0; a.ctr[2] = 0; a.ctr[4] = 0; a.ctr[5] = 0;
             if (!PLAIN && a.mode == kWfAutoNormPeer && a.epoch == 0)            // every CTA has read the old count by now
-                *reinterpret_cast<unsigned int *>(a.peer[a.rank] + 3) = a.ctr[3];
+                *reinterpret_cast<unsigned int *>(a.peer[a.rank] + 3) = a.ctr[6];
             __threadfence();
         }
     }
@@ -563,24 +584,28 @@ inline cudaError_t wf1024_attr() {
                                 (int)(BULK ? kWfSmemBulk : kWfSmemDirect));
 }
 inline int wf1024_setup() {
-    B2_CUDA((wf1024_attr<4, 0, true>())); B2_CUDA((wf1024_attr<8, 0, true>())); B2_CUDA((wf1024_attr<2, 0, true>()));
+    B2_CUDA((wf1024_attr<4, 0, true>()));
     B2_CUDA((wf1024_attr<4, 0, true, true>()));
+#ifdef B2_AB
+    B2_CUDA((wf1024_attr<8, 0, true>())); B2_CUDA((wf1024_attr<2, 0, true>()));
     B2_CUDA((wf1024_attr<4, 0, false>())); B2_CUDA((wf1024_attr<8, 0, false>())); B2_CUDA((wf1024_attr<2, 0, false>()));
 #ifdef B2_WF_ABLATION
     B2_CUDA((wf1024_attr<4, 1, false>())); B2_CUDA((wf1024_attr<4, 2, false>())); B2_CUDA((wf1024_attr<4, 3, false>()));
     B2_CUDA((wf1024_attr<4, 4, false>())); B2_CUDA((wf1024_attr<4, 7, false>()));
 #endif
+#endif
     return 0;
 }
 
+// Product path: 4-frame work items, bulk stores, single-frame items at the tail.  -DB2_AB builds read
+// B200VEC_WF_CHUNK (2|4|8), B200VEC_WF_BULK=0 (direct stores), B200VEC_WF_TAIL=0, B200VEC_WF_V (ablations).
 inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
     int chunk = kWfChunk, dbg = 0;
-    bool bulk = true;
-    if (const char *e = getenv("B200VEC_WF_CHUNK")) chunk = atoi(e);
-    if (const char *e = getenv("B200VEC_WF_V")) dbg = atoi(e);
-    if (const char *e = getenv("B200VEC_WF_BULK")) bulk = e[0] != '0';      // "0": direct STG stores (A/B)
-    bool tail = true;
-    if (const char *e = getenv("B200VEC_WF_TAIL")) tail = e[0] != '0';      // "0": no single-frame items at the end (A/B)
+    bool bulk = true, tail = true;
+    if (const char *e = ab_env("B200VEC_WF_CHUNK")) chunk = atoi(e);
+    if (const char *e = ab_env("B200VEC_WF_V")) dbg = atoi(e);
+    if (const char *e = ab_env("B200VEC_WF_BULK")) bulk = e[0] != '0';
+    if (const char *e = ab_env("B200VEC_WF_TAIL")) tail = e[0] != '0';
     B2_REQUIRE(chunk == 2 || chunk == 4 || chunk == 8, "B200VEC_WF_CHUNK must be 2, 4 or 8");
     const long long n_vec = a.plain ? 0 : a.place.hi - a.place.lo;
     const long long halves = (n_vec + 511) / 512;
@@ -599,6 +624,10 @@ inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
         B2_CUDA(cudaMemsetAsync(ctx->wf_ctr, 0, 16 * sizeof(unsigned int), st));
     }
     a.ctr = ctx->wf_ctr;
+    // The per-launch words are re-armed by the last CTA of every launch; zeroing them on the stream as well
+    // keeps a launch independent of whatever an earlier (failed, timed-out) launch left behind.  One fused
+    // launch may be in flight per context (the counters are the context's).
+    B2_CUDA(cudaMemsetAsync(ctx->wf_ctr, 0, 6 * sizeof(unsigned int), st));
     const long long cap = ctx->sm_count;
     const long long need = (a.n_chunks + kWfWarps - 1) / kWfWarps;
     const unsigned grid = (unsigned)(need < cap ? need : cap);
@@ -617,6 +646,10 @@ inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
         else                                                                                               \
             wf1024_kernel<C, D, B, false><<<grid, kWfThreads, (B) ? kWfSmemBulk : kWfSmemDirect, st>>>(a);        \
     } while (0)
+#ifndef B2_AB
+    (void)dbg; (void)bulk;
+    B2_WF_LAUNCH(4, 0, true);
+#else
     if (dbg == 0) {
         const int sel = (chunk == 8 ? 4 : chunk == 2 ? 2 : 0) | (bulk ? 1 : 0);
         switch (sel) {
@@ -637,9 +670,10 @@ inline int launch_wf1024(b200vec_ctx *ctx, WfArgs &a, cudaStream_t st) {
             default: B2_WF_LAUNCH(4, 7, false); break;
         }
 #else
-        return fail("launch_wf1024", "B200VEC_WF_V needs a -DB2_WF_ABLATION build");
+        return fail("launch_wf1024", "B200VEC_WF_V needs a -DB2_AB -DB2_WF_ABLATION build");
 #endif
     }
+#endif
 #undef B2_WF_LAUNCH
     B2_CUDA(cudaGetLastError());
     return 0;

@@ -112,13 +112,30 @@ def stft_slab(engine, vec, plan, window="hann", nperseg=1024, noverlap=512, nfft
                        n_frames=plan.frame_hi - plan.frame_lo, total_len=plan.total, out=out)
 
 
+TILE_SLOT = 62                 # bank slot the periodic tile is attached to (the vector build uses 0..31)
+REDUNDANT_MAX_SAMPLES = 16_000_000
+
+
 def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6, window="hann",
-                    scaling="density", out_vec=None, out_spec=None, peer=None):
+                    scaling="density", out_vec=None, out_spec=None, peer=None, tile="auto",
+                    redundant_max=REDUNDANT_MAX_SAMPLES):
     """Owned slab of the vector AND this rank's spectrogram columns (hann-1024/512 analysis STFT of
-    vector_analyzer/spectrogram_analysis.py:35-49) with the fused kernel: pass A (max, no stores)
-    -> [all-reduce MAX] -> one kernel that places, scales, stores the vector and transforms it
-    out of shared memory.  `plan` must be cut on hop boundaries: plan_slab(..., align=512).
-    Returns (vector [hi - lo], spectrogram [1024, frame_hi - frame_lo], maxsq or None)."""
+    vector_analyzer/spectrogram_analysis.py:35-49) with the fused kernel: one launch that finds the
+    max, places, scales, stores the vector and transforms it out of registers.  `plan` must be cut on
+    hop boundaries: plan_slab(..., align=512).
+    Returns (vector [hi - lo], spectrogram [1024, frame_hi - frame_lo], maxsq or None).
+
+    Normalisation across ranks (frame-major memory):
+      * the ranges that hold the global max (one common period of the packet trains + head and tail,
+        hostmath.max_eval_ranges) are short (<= redundant_max samples): EVERY rank evaluates all of them
+        inside its own launch — no exchange, no skew between GPUs, the same ONE launch as on a single GPU;
+      * otherwise each rank evaluates its share and the maxima are MAX-combined inside the kernel over
+        NVLink peer memory (`peer`, a PeerMax), or by `reduce_max` (NCCL / gloo all-reduce) between a
+        pass-A launch and the fused launch.
+    Periodic tiling (tile="auto" | True | False, hostmath.tile_plan): when the packet trains overlap
+    densely and share a common period T that fits the L2, the steady part of the slab repeats its first T
+    samples bit for bit; it is then placed from the vector itself (one L2 read per sample instead of one
+    per overlapping instance) by a second launch that names out_vec[x1 - T, x1) as an attached bank slot."""
     import torch
     from ._lib import BUILD_MAXONLY, BUILD_SCALE, BUILD_STORE
     nf = plan.frame_hi - plan.frame_lo
@@ -131,27 +148,61 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
     if out_spec is None:
         out_spec = engine.alloc_spectrogram(1024, nf, frame_major=True)
     frame_major = out_spec.dim() == 2 and out_spec.stride(0) == 1 and out_spec.stride(1) >= 1024
-    in_kernel_max = normalize and frame_major and (peer is not None or (plan.world == 1 and reduce_max is None))
+    rows = list(rows)
+    lengths = [engine.bank_len(r[3]) for r in rows]
+    full_ranges = H.max_eval_ranges(rows, lengths, plan.total) if normalize else []
+    if len(full_ranges) > 4:
+        full_ranges = [(0, plan.total)]
+    redundant = (normalize and frame_major and plan.world > 1 and
+                 sum(hi - lo for lo, hi in full_ranges) <= redundant_max)
+    in_kernel_max = normalize and frame_major and (redundant or peer is not None or
+                                                   (plan.world == 1 and reduce_max is None))
     descs, nd = engine.make_descs(rows, engine.free_flags(rows, plan.total) if in_kernel_max else None)
-    mode, norm_ranges = BUILD_STORE, None
-    if normalize and peer is not None and frame_major:
-        # multi-GPU, ONE launch per rank: this rank's share of pass A and the MAX exchange over NVLink
-        # peer memory both run inside the fused kernel (no NCCL call in the step)
-        norm_ranges = engine.max_ranges(rows, plan.total, plan.world, plan.rank)
-        if len(norm_ranges) > 4:
-            raise ValueError("too many max ranges for one launch")
-    elif normalize and plan.world == 1 and reduce_max is None and frame_major:
-        # single GPU: pass A runs inside the fused kernel (grid barrier), ONE launch for the step
-        norm_ranges = engine.max_ranges(rows, plan.total, 1, 0)
-        if len(norm_ranges) > 4:
-            norm_ranges = [(0, plan.total)]
+
+    tp = None
+    if tile and frame_major and nf > 0:
+        kw = {} if tile == "auto" else dict(min_density=0.0, min_gain=0.25)
+        tp = H.tile_plan(rows, lengths, plan.total, plan.lo, plan.hi, **kw)
+        if tp is not None and (tp["x2"] // 512 > plan.frame_hi or tp["x1"] >= tp["x2"]):
+            tp = None
+    # the launches: (lo, hi, frame_lo, frame_hi, descs, n_descs, use the slab's max logic?)
+    x1, x2 = (tp["x1"], tp["x2"]) if tp else (plan.hi, plan.hi)
+    f1 = min(plan.frame_hi, x1 // 512) if tp else plan.frame_hi
+
+    def vec_at(a):
+        return out_vec[a - plan.lo:]
+
+    def spec_at(f):
+        return out_spec[:, f - frame_lo:]
+
+    # ---- launch 1: [lo, x1) from the packet bank, with the normalisation
+    mode, norm_ranges, use_peer = BUILD_STORE, None, None
+    if in_kernel_max:
+        if redundant or plan.world == 1:
+            norm_ranges = full_ranges
+        else:
+            norm_ranges = H.split_ranges(full_ranges, plan.world, plan.rank)
+            use_peer = peer
+            if len(norm_ranges) > 4:
+                raise ValueError("too many max ranges for one launch")
     elif normalize:
         engine._maxsq.zero_()
         engine.max_pass(descs, nd, engine.max_ranges(rows, plan.total, plan.world, plan.rank))
         if reduce_max is not None:
             reduce_max(engine._maxsq)
         mode = BUILD_SCALE
-    engine.build_stft1024(descs, nd, plan.lo, plan.hi, out_vec, mode, frame_lo, nf, out_spec,
-                          window=window, fs=fs, scaling=scaling, norm_ranges=norm_ranges,
-                          peer=peer if norm_ranges is not None else None)
+    engine.build_stft1024(descs, nd, plan.lo, x1, out_vec, mode, frame_lo, f1 - frame_lo, out_spec,
+                          window=window, fs=fs, scaling=scaling, norm_ranges=norm_ranges, peer=use_peer)
+    if tp:
+        # ---- launch 2: [x1, x2) = the T samples before x1, repeated (already scaled: STORE)
+        t = tp["T"]
+        engine.bank_attach(TILE_SLOT, vec_at(x1 - t)[:t])
+        tdescs, tnd = engine.make_descs([(x1, t, tp["count"], TILE_SLOT)])
+        engine.build_stft1024(tdescs, tnd, x1, x2, vec_at(x1), BUILD_STORE, x1 // 512, x2 // 512 - x1 // 512,
+                              spec_at(x1 // 512), window=window, fs=fs, scaling=scaling)
+        # ---- launch 3: the tail [x2, hi) from the packet bank again
+        if x2 < plan.hi or x2 // 512 < plan.frame_hi:
+            engine.build_stft1024(descs, nd, x2, plan.hi, vec_at(x2), BUILD_SCALE if normalize else BUILD_STORE,
+                                  x2 // 512, plan.frame_hi - x2 // 512, spec_at(x2 // 512),
+                                  window=window, fs=fs, scaling=scaling)
     return out_vec, out_spec, (engine._maxsq if normalize else None)

@@ -56,14 +56,16 @@ class Engine:
     def bank_upload(self, slot, samples):
         """samples: numpy complex64 [L] (host) or torch complex64 CUDA tensor."""
         if isinstance(samples, torch.Tensor):
+            # device-to-device copy in stream order; torch's allocator frees `t` in stream order too
             t = samples.to(self.device, torch.complex64).contiguous()
             check(self.lib.b200vec_bank_upload(self._ctx, slot, self._ptr(t), t.numel(), 1, self._stream()))
-            torch.cuda.current_stream(self.device).synchronize()
         else:
+            # No synchronize: a copy from pageable memory returns once the source has been read, and an
+            # array that needed no conversion is the caller's own (pinned) buffer, which the caller keeps
+            # alive until the stream has passed — like any buffer handed to an asynchronous copy.
             a = np.ascontiguousarray(samples, dtype=np.complex64)
             check(self.lib.b200vec_bank_upload(self._ctx, slot, a.ctypes.data_as(C.c_void_p), a.size, 0,
                                                self._stream()))
-            torch.cuda.current_stream(self.device).synchronize()   # `a` may be a temporary
 
     def bank_resample(self, slot, n_out):
         check(self.lib.b200vec_bank_resample(self._ctx, slot, int(n_out), self._stream()))
@@ -71,6 +73,12 @@ class Engine:
     def bank_commit(self, slot, freq_hz=0.0, fs_hz=H.TARGET_SAMPLE_RATE):
         check(self.lib.b200vec_bank_shift(self._ctx, slot, float(freq_hz), float(fs_hz), self._stream()))
         self.launches += 1
+
+    def bank_attach(self, slot, samples):
+        """Make a complex64 CUDA tensor a committed bank slot WITHOUT copying it (b200vec_bank_attach):
+        the caller keeps `samples` alive and unchanged while launches that name the slot run."""
+        assert samples.is_cuda and samples.dtype == torch.complex64 and samples.is_contiguous()
+        check(self.lib.b200vec_bank_attach(self._ctx, slot, self._ptr(samples), samples.numel(), self._stream()))
 
     def bank_len(self, slot):
         n = C.c_int64()
@@ -130,28 +138,51 @@ class Engine:
         for lo, hi in ranges:
             self.build_pass(descs, n_descs, lo, hi, None, BUILD_MAXONLY, maxsq=maxsq)
 
+    def build_norm(self, descs, n_descs, lo, hi, out, ranges, maxsq=None):
+        """The normalised build in ONE launch (b200vec_build_norm): max |v|^2 over `ranges`, grid barrier,
+        scale pass.  maxsq receives max |v|^2."""
+        maxsq = self._maxsq if maxsq is None else maxsq
+        flat = [int(v) for r in ranges for v in r]
+        arr = (C.c_int64 * max(len(flat), 1))(*flat)
+        check(self.lib.b200vec_build_norm(self._ctx, descs, n_descs, int(lo), int(hi),
+                                          self._ptr(out) if out is not None else None, arr, len(flat) // 2,
+                                          self._ptr(maxsq), self._stream()))
+        self.launches += 1
+
     def build_vector(self, rows, total, normalize=True, lo=0, hi=None, out=None, reduce_max=None,
                      world=1, rank=0):
         """Samples [lo, hi) of the composite vector as a complex64 CUDA tensor.
 
-        normalize=True runs the two-pass recompute: pass A reduces max|v|^2 over the slab
-        (no stores), `reduce_max(tensor)` (if given) all-reduces that one double across
-        ranks, pass B recomputes and stores v * (1/max).  Returns (vector, maxsq tensor)."""
+        normalize=True: max |v|^2 and the scaled stores are ONE launch (pass A over the sample ranges
+        that hold the global max, grid barrier, pass B) unless `reduce_max(tensor)` is given — then pass
+        A is its own launch, reduce_max all-reduces that one double across ranks, and pass B recomputes
+        and stores v * (1/max).  Returns (vector, maxsq tensor)."""
         hi = total if hi is None else hi
         n = hi - lo
         if out is None:
             out = torch.empty(max(n, 0), dtype=torch.complex64, device=self.device)
-        descs, nd = self.make_descs(rows)
         if not normalize:
+            descs, nd = self.make_descs(rows)
             self.build_pass(descs, nd, lo, hi, out, BUILD_STORE)
             return out, None
+        if reduce_max is None:
+            if lo != 0 or hi != total:
+                descs, nd = self.make_descs(rows)
+                ranges = [(lo, hi)]                                          # a lone sub-range: its own max
+            else:
+                descs, nd = self.make_descs(rows, self.free_flags(rows, total))
+                ranges = self.max_ranges(rows, total, 1, 0)
+                if len(ranges) > 4:
+                    ranges = [(0, total)]
+            if n > 0:
+                self.build_norm(descs, nd, lo, hi, out, ranges)
+            else:
+                self._maxsq.zero_()
+            return out, self._maxsq
+        descs, nd = self.make_descs(rows)
         self._maxsq.zero_()
-        if reduce_max is None and (lo != 0 or hi != total):
-            self.build_pass(descs, nd, lo, hi, None, BUILD_MAXONLY)      # a lone sub-range: its own max
-        else:
-            self.max_pass(descs, nd, self.max_ranges(rows, total, world, rank))
-        if reduce_max is not None:
-            reduce_max(self._maxsq)
+        self.max_pass(descs, nd, self.max_ranges(rows, total, world, rank))
+        reduce_max(self._maxsq)
         self.build_pass(descs, nd, lo, hi, out, BUILD_SCALE)
         return out, self._maxsq
 
@@ -286,30 +317,121 @@ class Engine:
         v = self.select_ranks(x, [lo, hi], positive_only)
         return H.lerp(v[0], v[1], gamma)
 
+    def select_begin(self, x, use_abs=False):
+        """13-bit key histogram of a float32 CUDA tensor in one read (b200vec_select_begin).
+        Returns the number of elements > 0 (after the optional abs)."""
+        n_pos = C.c_int64()
+        check(self.lib.b200vec_select_begin(self._ctx, self._ptr(x), x.numel(), int(use_abs), C.byref(n_pos),
+                                            self._stream()))
+        self.launches += 1
+        return n_pos.value
+
+    def select_finish(self, x, ranks):
+        """Exact values at `ranks` (positions in the ascending sort of ALL elements of the tensor
+        select_begin was called on): bin pick on the host, one compaction read, exact select on the
+        candidates (b200vec_select_finish)."""
+        ranks = [int(r) for r in ranks]
+        arr = (C.c_int64 * len(ranks))(*ranks)
+        vals = (C.c_float * len(ranks))()
+        check(self.lib.b200vec_select_finish(self._ctx, self._ptr(x), x.numel(), arr, len(ranks), vals,
+                                             self._stream()))
+        self.launches += 8
+        return np.asarray(list(vals), dtype=np.float32)
+
     def normalize_spectrogram(self, s, low_percentile=10.0, high_percentile=95.0, max_dynamic_range=25):
         """Device form of utils.normalize_spectrogram (utils.py:356-404) for a float32 CUDA
-        tensor: returns (Sxx_db tensor, vmin, vmax)."""
+        tensor: returns (Sxx_db tensor, vmin, vmax).
+
+        10*log10(|S| + floor) is monotone in |S|, so every order statistic the function needs — the 5th
+        percentile of the positive elements (the floor) and the low / high percentiles, minimum and maximum
+        of the dB image — is an order statistic of |S|: all eight ranks come out of ONE selection (two
+        full reads of S), the dB image is written once, and the six dB values are the dB of six |S| values."""
         flat = s.contiguous().view(-1)
-        floor_ = self.percentile(flat, 5, positive_only=True)
-        floor_ = 1e-12 if floor_ is None else floor_
-        floor_ = max(floor_, 1e-12)
-        db = self.db(flat, floor_).view(s.shape)
-        dflat = db.view(-1)
-        n = dflat.numel()
+        n = flat.numel()
+        if n == 0:
+            return torch.empty_like(s), 0, 0
+        n_pos = self.select_begin(flat, use_abs=True)
         lo1, hi1, g1 = H.percentile_ranks(n, low_percentile, np.float32)
         lo2, hi2, g2 = H.percentile_ranks(n, high_percentile, np.float32)
-        v = self.select_ranks(dflat, [lo1, hi1, lo2, hi2, 0, n - 1])
-        vmin, vmax = H.lerp(v[0], v[1], g1), H.lerp(v[2], v[3], g2)
-        vmin, vmax = H.colour_limits(vmin, vmax, v[4], v[5], max_dynamic_range)
+        ranks = [lo1, hi1, lo2, hi2, 0, n - 1]
+        if n_pos > 0:
+            lo0, hi0, g0 = H.percentile_ranks(n_pos, 5, np.float32)
+            ranks += [n - n_pos + lo0, n - n_pos + hi0]          # the positive elements are the top n_pos of |S|
+        v = self.select_finish(flat, ranks)
+        floor_ = H.lerp(v[6], v[7], g0) if n_pos > 0 else 1e-12
+        floor_ = max(floor_, 1e-12)
+        db = self.db(flat, floor_).view(s.shape)
+        six = self.db(torch.from_numpy(v[:6].copy()).to(self.device), floor_).cpu().numpy()
+        vmin, vmax = H.lerp(six[0], six[1], g1), H.lerp(six[2], six[3], g2)
+        vmin, vmax = H.colour_limits(vmin, vmax, six[4], six[5], max_dynamic_range)
         return db, vmin, vmax
 
-    # ------------------------------------------------------------------ .wv payload
-    def wv_quantize(self, x, out=None):
-        x = x.contiguous()
-        out = torch.empty(2 * x.numel(), dtype=torch.int16, device=self.device) if out is None else out
-        check(self.lib.b200vec_wv_quantize(self._ctx, self._ptr(x), x.numel(), self._ptr(out), self._stream()))
+    def decimate(self, x, stride):
+        """x[::stride] as a compact complex64 tensor (b200vec_decimate; utils.py:192-195)."""
+        x = x.reshape(-1)
+        n_out = (x.numel() + stride - 1) // stride
+        out = torch.empty(n_out, dtype=torch.complex64, device=self.device)
+        check(self.lib.b200vec_decimate(self._ctx, self._ptr(x), x.numel(), int(stride), self._ptr(out), self._stream()))
         self.launches += 1
         return out
+
+    # ------------------------------------------------------------------ scenario batch
+    def batch_prepare(self, scenarios, fs_hz):
+        """scenarios: per vector a list of (start, period, count, src_slot, freq_hz[, free_flag]) — every
+        distinct (src_slot, freq_hz) is shifted once, in one launch (b200vec_batch_prepare)."""
+        from ._lib import BatchPkt
+        n_pk = sum(len(sc) for sc in scenarios)
+        pk = (BatchPkt * max(n_pk, 1))()
+        first = (C.c_int32 * (len(scenarios) + 1))()
+        i = 0
+        for v, sc in enumerate(scenarios):
+            first[v] = i
+            for row in sc:
+                start, period, count, slot, freq = row[:5]
+                pk[i] = BatchPkt(int(start), int(period), int(count), int(slot),
+                                 1 if (len(row) > 5 and row[5]) else 0, float(freq))
+                i += 1
+        first[len(scenarios)] = i
+        check(self.lib.b200vec_batch_prepare(self._ctx, pk, first, len(scenarios), float(fs_hz), self._stream()))
+        self.launches += 1
+        self._batch_n = len(scenarios)
+
+    def batch_build(self, total, normalize=True, out=None, maxsq=None):
+        """All vectors of the prepared batch in ONE launch (b200vec_batch_build): returns
+        (complex64 [n_vectors, total] CUDA tensor, maxsq float64 [n_vectors] or None)."""
+        nv = self._batch_n
+        ld = (total + 1) // 2 * 2
+        if out is None:
+            out = torch.empty((nv, max(ld, 2)), dtype=torch.complex64, device=self.device)
+        if normalize and maxsq is None:
+            maxsq = torch.empty(nv, dtype=torch.float64, device=self.device)
+        check(self.lib.b200vec_batch_build(self._ctx, int(total), self._ptr(out), out.stride(0), int(bool(normalize)),
+                                           self._ptr(maxsq) if normalize else None, self._stream()))
+        self.launches += 1
+        return out[:, :total], (maxsq if normalize else None)
+
+    def peer_status(self):
+        """1 when an in-kernel peer MAX exchange on this engine timed out since the last call."""
+        st = C.c_int()
+        check(self.lib.b200vec_peer_status(self._ctx, C.byref(st), self._stream()))
+        return st.value
+
+    # ------------------------------------------------------------------ .wv payload
+    def wv_quantize(self, x, out=None, pre_scale=1.0):
+        x = x.contiguous()
+        out = torch.empty(2 * x.numel(), dtype=torch.int16, device=self.device) if out is None else out
+        check(self.lib.b200vec_wv_quantize(self._ctx, self._ptr(x), x.numel(), float(pre_scale), self._ptr(out),
+                                           self._stream()))
+        self.launches += 1
+        return out
+
+    def power_stats(self, x, pre_scale=1.0):
+        """(max |y|^2, sum fl32(|y|)^2) of y = x * pre_scale as Python floats (b200vec_power_stats)."""
+        x = x.contiguous()
+        st = (C.c_double * 2)()
+        check(self.lib.b200vec_power_stats(self._ctx, self._ptr(x), x.numel(), float(pre_scale), st, self._stream()))
+        self.launches += 1
+        return float(st[0]), float(st[1])
 
 
 _ENGINES = {}

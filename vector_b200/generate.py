@@ -82,6 +82,58 @@ def build_vector_device(configs, total_samples, normalize=True, packets=None,
     return vec, make_markers(configs, info, rows, fs), [r[2] for r in rows], maxsq
 
 
+BATCH_SLOT_BASE = 32          # source packets of a scenario batch live in bank slots 32..61
+
+
+def build_batch_device(scenarios, total_samples, normalize=True, packets=None, fs=H.TARGET_SAMPLE_RATE,
+                       resample=False, engine=None):
+    """A sweep of independent scenario vectors (BASELINE.json configs[4]) — what the reference produces by
+    running generate_vector once per scenario (unified_gui.py:1722-1782 in a loop) — as TWO device calls:
+    every distinct (packet, frequency shift) is shifted once in one launch, then ONE launch places,
+    normalises (each vector by its own max) and stores all vectors.
+
+    scenarios: list of config lists (get_config() dicts, like build_vector_device's `configs`).
+    packets: {file: (samples, pre_samples)} for the distinct files (default: load_packet_info per file).
+    Returns (vectors CUDA complex64 [n_vectors, total_samples], markers per vector, instance counts per
+    vector, maxsq CUDA float64 [n_vectors] or None)."""
+    eng = engine or get_engine()
+    files = []
+    for cfgs in scenarios:
+        for cfg in cfgs:
+            key = (cfg["file"], cfg.get("sample_rate", fs) if resample else fs)
+            if key not in files:
+                files.append(key)
+    if len(files) > 30:
+        raise ValueError("a scenario batch draws from at most 30 distinct packets")
+    src = {}
+    for i, (name, rate) in enumerate(files):
+        y, pre = packets[name] if packets is not None else api.load_packet_info(name)
+        slot = BATCH_SLOT_BASE + i
+        eng.bank_upload(slot, y)
+        if rate != fs:                                                    # main.py:236-237
+            eng.bank_resample(slot, int(len(y) * (fs / rate)))
+        src[(name, rate)] = (slot, eng.bank_len(slot), pre)
+    batch, all_rows, all_info = [], [], []
+    for cfgs in scenarios:
+        info, rows = [], []
+        for i, cfg in enumerate(cfgs):
+            slot, length, pre = src[(cfg["file"], cfg.get("sample_rate", fs) if resample else fs)]
+            period = H.period_samples(cfg["period"], fs)
+            if period <= 0:
+                raise ValueError(f"Invalid period for packet {i+1}")
+            start = H.start_offset(cfg["start_time"], pre, fs)
+            rows.append((start, period, H.instance_count(start, period, length, total_samples), slot))
+            info.append((length, pre))
+        flags = H.free_instance_flags(rows, [l for l, _ in info], total_samples) if normalize else [False] * len(rows)
+        batch.append([(s, p, k, slot, cfg["freq_shift"], fl) for (s, p, k, slot), cfg, fl in zip(rows, cfgs, flags)])
+        all_rows.append(rows)
+        all_info.append(info)
+    eng.batch_prepare(batch, fs)
+    vecs, maxsq = eng.batch_build(total_samples, normalize)
+    markers = [make_markers(cfgs, info, rows, fs) for cfgs, info, rows in zip(scenarios, all_info, all_rows)]
+    return vecs, markers, [[r[2] for r in rows] for rows in all_rows], maxsq
+
+
 def build_vector(configs, total_samples, normalize=True, packets=None, fs=H.TARGET_SAMPLE_RATE,
                  resample=False):
     """numpy-facing build: (vector complex64 ndarray, markers, instance_counts)."""
@@ -145,8 +197,8 @@ def make_unified_generate_vector(ns):
                 vector = None
             else:
                 output_path = f"vector_{timestamp}.mat"
-                vector = vec_dev.cpu().numpy()
-                api.save_vector(vector, output_path)
+                api.save_vector(vec_dev, output_path)         # planes split on the device, streamed to the file
+                vector = None
             print(f"Vector saved to {output_path}")
 
             validation_text, detailed = self.validate_packet_timing(markers, self.packet_configs)
@@ -195,7 +247,7 @@ def make_main_generate_vector(ns):
             if output_format == "wv":
                 api.save_vector_wv(vec_dev, 'data/output_vector.wv', FS)
             else:
-                api.save_vector(vec_dev.cpu().numpy(), 'data/output_vector.mat')
+                api.save_vector(vec_dev, 'data/output_vector.mat')
             center_freq = 0
             if freq_shifts:
                 center_freq = (min(freq_shifts) + max(freq_shifts)) / 2

@@ -409,40 +409,78 @@ def frame_range_for_slab(lo, hi, total, stride, nperseg, hop, n_frames):
 
 
 # --------------------------------------------------------------------------- max-abs pass
-def max_eval_ranges(rows, lengths, total):
-    """Sample ranges over which max|v| has to be evaluated to get the max over [0, total).
+def common_period(rows, lengths, total):
+    """(A, B, T) such that the composite repeats bit for bit with period T on [A, B + T):
+    v(i + T) == v(i) for A <= i < B — or None when the trains share no usable period.
 
     The composite is a sum of periodic trains, v(i) = sum_p sum_k y_p[i - s_p - k P_p]
     (unified_gui.py:1757-1769).  Packet p's train repeats exactly — same y values added in the
     same (packet, instance) order, hence bit-identical float32 sums — under a shift by its period
     wherever no instance is entering or leaving:
         c_p(i + P_p) == c_p(i)   for   max(0, s_p + L_p - P_p) <= i < s_p + (K_p - 1) P_p.
-    With T = lcm(P_p) that gives v(i + T) == v(i) on [A, B),
-        A = max_p max(0, s_p + L_p - P_p),   B = min_p (s_p + K_p P_p - T),
-    so every value taken on [A, B + T) is already taken on [A, A + T) and
-        max over [0, total) = max over [0, A + T) U [B + T, total).
-    Falls back to the whole vector when the trains share no usable period (a packet placed
-    once, T too long, B <= A).  rows: (start, period, count, slot); lengths: packet lengths.
-    Returns a list of disjoint, ascending (lo, hi)."""
-    whole = [(0, int(total))] if total > 0 else []
+    With T = lcm(P_p):  A = max_p max(0, s_p + L_p - P_p),   B = min_p (s_p + K_p P_p - T).
+    rows: (start, period, count, slot); lengths: packet lengths."""
     live = [(int(s), int(p), int(k), int(n)) for (s, p, k, _), n in zip(rows, lengths) if k > 0]
-    if not live or total <= 0:
-        return whole
-    if any(k < 2 for _, _, k, _ in live):
-        return whole
+    if not live or total <= 0 or any(k < 2 for _, _, k, _ in live):
+        return None
     t = 1
     for _, p, _, _ in live:
         t = t * p // math.gcd(t, p)
         if t >= total:
-            return whole
+            return None
     a = max(max(0, s + n - p) for s, p, _, n in live)
     b = min(s + k * p - t for s, p, k, _ in live)
-    if b <= a or a + t >= b + t or a + t >= total:
+    if b <= a or a + t >= total:
+        return None
+    return a, b, t
+
+
+def max_eval_ranges(rows, lengths, total):
+    """Sample ranges over which max|v| has to be evaluated to get the max over [0, total).
+
+    With (A, B, T) = common_period(...): every value taken on [A, B + T) is already taken on
+    [A, A + T), so   max over [0, total) = max over [0, A + T) U [B + T, total).
+    Falls back to the whole vector when the trains share no usable period (a packet placed
+    once, T too long, B <= A).  Returns a list of disjoint, ascending (lo, hi)."""
+    whole = [(0, int(total))] if total > 0 else []
+    cp = common_period(rows, lengths, total)
+    if cp is None:
         return whole
+    a, b, t = cp
     out = [(0, a + t)]
     if b + t < total:
         out.append((b + t, int(total)))
     return out
+
+
+def tile_plan(rows, lengths, total, lo, hi, max_tile_samples=6_000_000, min_density=1.5, min_gain=1.0):
+    """Periodic tiling of the slab [lo, hi) (multiples of 512 except at the vector's end): when the packet
+    trains share a common period T that fits the L2 (max_tile_samples * 8 bytes) and overlap densely
+    (sum_p L_p / P_p >= min_density instance reads per output sample), the steady part of the slab is the
+    bit-exact repetition of its first T samples —
+        v(i) == v(i - T)   for   A + T <= i < B + T      (common_period)
+    — so it can be PLACED like one pseudo-packet of length and period T read from the vector itself
+    (one read per sample instead of one per overlapping instance).  Returns None, or
+    dict(x1, x2, T, count): [lo, x1) and [x2, hi) are built from the packet bank, [x1, x2) from
+    out[x1 - T, x1) placed at x1, x1 + T, ... (`count` instances, the last also covering the 512-sample
+    halo past x2); x1 and x2 are multiples of 512."""
+    cp = common_period(rows, lengths, total)
+    if cp is None:
+        return None
+    a, b, t = cp
+    if t > max_tile_samples:
+        return None
+    density = sum(n / p for (_, p, k, _), n in zip(rows, lengths) if k > 0)
+    if density < min_density:
+        return None
+    x1 = -(-(max(lo, a) + t) // 512) * 512
+    lim = b + t                                       # v(i) == v(i - T) holds for i < lim
+    x2 = min(hi, (lim - 512) // 512 * 512)
+    if hi % 512 and x2 == hi:
+        x2 = hi // 512 * 512
+    if x2 - x1 < max(512, int(min_gain * t)):
+        return None
+    return dict(x1=x1, x2=x2, T=t, count=-(-(x2 + 512 - x1) // t))
 
 
 def split_ranges(ranges, world, rank):
