@@ -1,0 +1,359 @@
+"""GPU tests of the round-2 components, all through the C-ABI: the warp-per-span builder and the one-launch
+normalised build, the scenario batch, periodic tiling through an attached bank slot, the fast order
+statistics, the compact-decimation preview, the save path (streamed .mat / .wv, mat2wv's normalize branch)
+and the degenerate cases of detect_packet_bounds."""
+import os
+
+import numpy as np
+import pytest
+import scipy.io as sio
+
+from oracle import ref_port as O
+from tests import parity as P
+from tests.golden import cases
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def eng():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from vector_b200.engine import get_engine
+    return get_engine(0)
+
+
+def _rows(eng, cfgs, pk, n, fs=56e6, resample=False):
+    from vector_b200 import generate
+    info = generate.prepare_bank(eng, cfgs, pk, fs, resample=resample)
+    return generate.placement_rows(cfgs, info, n, fs), info
+
+
+# ------------------------------------------------------------------------------ span kernel / build_norm
+@pytest.mark.parametrize("n", [1, 2, 511, 512, 513, 2047, 2048, 2049, 300_001, 1_000_000])
+def test_one_launch_normalised_build_equals_two_pass(eng, n):
+    """b200vec_build_norm (max pass, grid barrier, scale pass in one cooperative launch) == MAXONLY launch +
+    SCALE launch, bit for bit, and both meet the oracle; ragged lengths cover partial last halves."""
+    from vector_b200._lib import BUILD_MAXONLY, BUILD_SCALE
+    cfgs = O._rows_to_configs([("noise", 0.5, 0.01, 0.003), ("multitone", -2, 0.4, 0.0), ("bpsk", 1, 0.13, 0.05)])
+    pk = [(y[:700], pre) for y, pre in O.packets_for(cfgs)]
+    want, _, _, max_ref = O.build_vector(pk, cfgs, n, True)
+    rows, _ = _rows(eng, cfgs, pk, n)
+    one, m1 = eng.build_vector(rows, n, True)
+    m1 = m1.clone()
+    descs, nd = eng.make_descs(rows)
+    m2 = torch.zeros(1, dtype=torch.float64, device=eng.device)
+    eng.build_pass(descs, nd, 0, n, None, BUILD_MAXONLY, maxsq=m2)
+    two = torch.empty(n, dtype=torch.complex64, device=eng.device)
+    eng.build_pass(descs, nd, 0, n, two, BUILD_SCALE, maxsq=m2)
+    assert torch.equal(m1, m2) and torch.equal(one, two)
+    if np.any(want):
+        assert P.rel_l2(one.cpu().numpy(), want) <= 3e-7
+        assert abs(np.float32(np.sqrt(m1.item())) - max_ref) <= np.spacing(max_ref)
+    else:
+        assert not torch.any(one != 0)
+
+
+def test_max_pass_ignores_samples_past_the_range(eng):
+    """a max-only pass over [lo, hi) with hi cutting through an instance whose larger samples lie
+    just past hi must not see them (the last partial span is masked before the fp64 evaluation)."""
+    from vector_b200._lib import BUILD_MAXONLY
+    y = np.full(2000, 0.1 + 0.1j, np.complex64)
+    y[1000:] = 5.0 + 5.0j                                   # the big part starts at packet index 1000
+    eng.bank_upload(0, y)
+    eng.bank_commit(0, 0.0, 56e6)
+    rows = [(0, 10_000, 1, 0)]
+    descs, nd = eng.make_descs(rows)
+    for hi in (1000, 999, 513, 1001):
+        m = torch.zeros(1, dtype=torch.float64, device=eng.device)
+        eng.build_pass(descs, nd, 0, hi, None, BUILD_MAXONLY, maxsq=m)
+        want = np.max(np.abs(y[:hi].astype(np.complex128)) ** 2)
+        assert abs(m.item() - want) <= 1e-6 * want, (hi, m.item(), want)
+    sub, msq = eng.build_vector(rows, 20_000, True, lo=0, hi=1000)          # a lone sub-range: its own max
+    assert abs(np.sqrt(msq.item()) - abs(y[0])) <= 1e-6
+
+
+def test_unshifted_dense_overlap_bit_exact_span_kernel(eng):
+    """Period far shorter than the packet (hundreds of instances per sample), odd length: only float32 adds in
+    the reference's order — bit-exact, normalised or not."""
+    from vector_b200 import generate
+    cfgs = O._rows_to_configs([("noise", 0, 0.002, 0.003), ("multitone", 0, 0.05, 0.0)])
+    pk = O.packets_for(cfgs)
+    n = 200_003
+    want = O.build_vector(pk, cfgs, n, False)[0]
+    vec, _, counts, _ = generate.build_vector_device(cfgs, n, False, packets=pk, engine=eng)
+    assert counts[0] > 1000 and np.array_equal(vec.cpu().numpy(), want)
+    nv, _, _, msq = generate.build_vector_device(cfgs, n, True, packets=pk, engine=eng)
+    m = np.float32(np.sqrt(msq.item()))
+    assert np.array_equal(nv.cpu().numpy(), want / m)
+
+
+# ------------------------------------------------------------------------------ scenario batch
+@pytest.mark.parametrize("normalize", [True, False])
+def test_batch_equals_single_builds(eng, normalize):
+    """b200vec_batch_prepare + b200vec_batch_build: 12 scenario vectors (shared and distinct shifts, an empty
+    scenario, an unshifted packet, odd length) == 12 single-vector builds, bit for bit, and the oracle."""
+    from vector_b200 import generate, synth
+    n = 700_001
+    bank = synth.bank(56e6)
+    scen = [synth.configs(synth.cfg5_rows(v)) for v in range(9)]
+    scen.append(synth.configs([("tone", 0, 1.3, 0.0), ("noise", 4.5, 0.4, 0.2)]))      # unshifted + self-overlap
+    scen.append(synth.configs([("chirp", -3, 1.0, 13.0)]))                             # starts past the end: no instance fits
+    scen.append(scen[3])                                                               # a repeated scenario: shared shifts
+    packets = {c["file"]: bank[c["kind"]] for cfgs in scen for c in cfgs}
+    vecs, markers, counts, maxsq = generate.build_batch_device(scen, n, normalize, packets=packets, engine=eng)
+    assert vecs.shape == (len(scen), n)
+    assert (maxsq is None) == (not normalize)
+    for v, cfgs in enumerate(scen):
+        pk = [packets[c["file"]] for c in cfgs]
+        one, mk, cnt, m1 = generate.build_vector_device(cfgs, n, normalize, packets=pk, engine=eng)
+        assert counts[v] == cnt and [m[0] for m in markers[v]] == [m[0] for m in mk]
+        assert torch.equal(vecs[v], one), v
+        if normalize:
+            assert maxsq[v].item() == m1.item()
+        want = O.build_vector(pk, cfgs, n, normalize)[0]
+        if np.any(want):
+            assert P.rel_l2(vecs[v].cpu().numpy(), want) <= 3e-7
+        else:
+            assert not torch.any(vecs[v] != 0)
+    assert torch.equal(vecs[11], vecs[3])
+
+
+def test_batch_requires_prepare_and_validates(eng):
+    from vector_b200._lib import B200VecError
+    from vector_b200.engine import Engine
+    e2 = Engine(0)
+    e2._batch_n = 1
+    with pytest.raises(B200VecError, match="no prepared batch"):
+        e2.batch_build(1000)
+    with pytest.raises(B200VecError, match="source slot is empty"):
+        e2.batch_prepare([[(0, 10, 1, 40, 0.0)]], 56e6)
+    e2.close()
+
+
+# ------------------------------------------------------------------------------ periodic tiling
+def _cfg4_case(ms):
+    from vector_b200 import synth
+    fs = 200e6
+    cfgs, pk = synth.scenario(synth.CFG4_ROWS, 56e6)
+    for c in cfgs:
+        c["sample_rate"] = 56e6
+    return fs, cfgs, pk, int(ms * 1e-3 * fs)
+
+
+@pytest.mark.parametrize("world", [1, 2, 3])
+def test_periodic_tiling_is_bit_exact(eng, world):
+    """dist.build_stft_slab with tile=True (steady part of a dense slab placed from the vector itself through an
+    attached bank slot: ONE L2 read per sample) == tile=False (every overlapping instance gathered), bit for bit,
+    vector and spectrogram, on a shortened cfg4 (60 ms: 5 common periods of 12 ms) and per rank of a sharded run."""
+    from vector_b200 import dist as vdist, hostmath as H
+    fs, cfgs, pk, n = _cfg4_case(60)
+    rows, info = _rows(eng, cfgs, pk, n, fs, resample=True)
+    full_plan = vdist.plan_slab(n, 1, 0, 1024, 512, 1, align=512)
+    ref_vec, ref_spec, ref_m = vdist.build_stft_slab(eng, rows, full_plan, True, None, fs=fs, tile=False)
+    ref_vec, ref_spec, ref_m = ref_vec.clone(), ref_spec.clone(), ref_m.clone()
+    want = O.build_vector(pk, cfgs, n, True, fs=fs, resample=True)[0]
+    assert P.rel_l2(ref_vec.cpu().numpy(), want) <= P.VEC_REL_L2
+    tiled = 0
+    for rank in range(world):
+        plan = vdist.plan_slab(n, world, rank, 1024, 512, 1, align=512)
+        tp = H.tile_plan(rows, [i[0] for i in info], n, plan.lo, plan.hi, min_density=0.0, min_gain=0.25)
+        tiled += tp is not None
+        vec, spec, m = vdist.build_stft_slab(eng, rows, plan, True, None, fs=fs, tile=True, redundant_max=1 << 40)
+        assert torch.equal(m, ref_m)
+        assert torch.equal(vec, ref_vec[plan.lo:plan.hi]), rank
+        assert torch.equal(spec, ref_spec[:, plan.frame_lo:plan.frame_hi]), rank
+    assert tiled >= 1
+    if world == 1:
+        tp = H.tile_plan(rows, [i[0] for i in info], n, 0, n, min_density=0.0, min_gain=0.25)
+        assert tp["T"] == 2_400_000 and tp["x1"] % 512 == 0 and tp["x2"] % 512 == 0 and tp["x2"] - tp["x1"] > 2_400_000
+
+
+def test_attached_slot_places_like_an_uploaded_packet(eng):
+    """b200vec_bank_attach: caller-owned device memory as a bank slot, no copy."""
+    from vector_b200._lib import B200VecError, BUILD_STORE
+    rng = np.random.default_rng(5)
+    y = (rng.standard_normal(3001) + 1j * rng.standard_normal(3001)).astype(np.complex64)
+    n = 50_001
+    eng.bank_upload(0, y)
+    eng.bank_commit(0, 0.0, 56e6)
+    rows = [(17, 1900, H_count(17, 1900, 3001, n), 0)]
+    a, _ = eng.build_vector(rows, n, False)
+    dev = torch.from_numpy(y).to(eng.device)
+    eng.bank_attach(5, dev)
+    assert eng.bank_len(5) == 3001 and np.array_equal(eng.bank_download(5), y)
+    b, _ = eng.build_vector([(17, 1900, rows[0][2], 5)], n, False)
+    assert torch.equal(a, b)
+    spec = eng.alloc_spectrogram(1024, 8, frame_major=False)                  # the C-order tile kernel needs both bank copies
+    descs, nd = eng.make_descs([(0, 4096, 1, 5)])
+    with pytest.raises(B200VecError, match="attached"):
+        eng.build_stft1024(descs, nd, 0, 4096, torch.empty(4096, dtype=torch.complex64, device=eng.device),
+                           BUILD_STORE, 0, 7, spec)
+
+
+def H_count(start, period, length, total):
+    from vector_b200 import hostmath as H
+    return H.instance_count(start, period, length, total)
+
+
+# ------------------------------------------------------------------------------ fast order statistics
+def test_select_begin_finish_is_exact(eng):
+    rng = np.random.default_rng(12)
+    for n in (1, 2, 33, 5000, 1_000_003, 9_000_001):
+        a = (rng.standard_normal(n) * 10 ** rng.uniform(-12, 2, n)).astype(np.float32)
+        a[rng.integers(0, n, n // 3)] = 0.0                    # heavy with exact zeros, like a spectrogram
+        a[rng.integers(0, n, n // 50)] = -0.0
+        for use_abs in (True, False):
+            x = np.abs(a) if use_abs else a
+            srt = np.sort(x)
+            d = torch.from_numpy(a).to(eng.device)
+            n_pos = eng.select_begin(d, use_abs=use_abs)
+            assert n_pos == int(np.count_nonzero(x > 0))
+            ranks = sorted({0, n - 1, n // 2, n // 3, min(n - 1, n // 2 + 1), (n - n_pos) if n_pos else 0,
+                            min(n - 1, n - n_pos + n_pos // 20)})[:8]
+            got = eng.select_finish(d, ranks)
+            assert np.array_equal(got, srt[ranks]), (n, use_abs, got, srt[ranks])
+
+
+def test_select_finish_falls_back_on_massive_ties(eng):
+    """One non-zero value repeated through most of the array: the bins in question hold too many candidates and
+    the exact 3-level select on the whole array takes over; still exact."""
+    n = 12_000_000
+    a = np.full(n, 3.25e-7, np.float32)
+    a[::7] = 1.5e-7
+    a[::1001] = -2.0
+    d = torch.from_numpy(a).to(eng.device)
+    srt = np.sort(np.abs(a))
+    assert eng.select_begin(d, use_abs=True) == n
+    ranks = [0, n // 10, n // 2, n - 1]
+    assert np.array_equal(eng.select_finish(d, ranks), srt[ranks])
+    from vector_b200._lib import B200VecError
+    with pytest.raises(B200VecError, match="select_begin"):
+        eng.select_finish(torch.zeros(10, device=eng.device), [0])
+
+
+@pytest.mark.parametrize("name", ["wf_2p5ms_shift_norm", "overlap_5ms", "cfg1_100ms"])
+def test_normalize_spectrogram_device_matches_oracle(eng, name):
+    """The one-selection form of normalize_spectrogram (all eight ranks are ranks of |S|) on preview AND
+    full-rate maps, default and plot_spectrogram's (5, 95, 25) arguments, both memory layouts."""
+    import vector_b200 as vb
+    from vector_b200 import generate
+    case = cases.build_cases()[name]
+    pk = O.packets_for(case["configs"])
+    n = O.total_samples_unified(case["length_ms"])
+    want = O.build_vector(pk, case["configs"], n, case["normalize"])[0]
+    dev = torch.from_numpy(want).to(eng.device)
+    _, _, S1 = vb.create_spectrogram_device(dev, 56e6, time_resolution_us=1, engine=eng)
+    _, _, S2 = vb.full_rate_spectrogram_device(dev, 56e6, engine=eng)               # frame-major memory
+    for S in (S1, S2):
+        Sh = np.ascontiguousarray(S.cpu().numpy())
+        for args in ((5, 95, 25), (10.0, 95.0, 25)):
+            db_r, vmin_r, vmax_r = O.normalize_spectrogram(Sh, *args)
+            db, vmin, vmax = eng.normalize_spectrogram(S, *args)
+            assert db.shape == S.shape
+            assert np.max(np.abs(db.cpu().numpy() - db_r)) <= 1e-4
+            assert abs(vmin - vmin_r) <= 1e-4 and abs(vmax - vmax_r) <= 1e-4
+    z = torch.zeros((64, 10), device=eng.device)
+    db, vmin, vmax = eng.normalize_spectrogram(z)
+    db_r, vmin_r, vmax_r = O.normalize_spectrogram(np.zeros((64, 10), np.float32))
+    assert np.max(np.abs(db.cpu().numpy() - db_r)) <= 1e-4 and abs(vmin - vmin_r) <= 1e-4 and abs(vmax - vmax_r) <= 1e-4
+
+
+# ------------------------------------------------------------------------------ preview through the compact copy
+def test_decimated_preview_equals_strided_transform(eng):
+    """create_spectrogram on a heavy signal: x[::factor] gathered once (b200vec_decimate) and transformed at
+    stride 1 == the strided transform of round 1, bit for bit; and the oracle bar."""
+    import vector_b200 as vb
+    from vector_b200 import hostmath as H
+    rng = np.random.default_rng(3)
+    n = 5_600_123
+    tt = np.arange(n) / 56e6
+    x = (np.exp(2j * np.pi * 1.1e6 * tt) + 0.02 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))).astype(np.complex64)
+    x[2_000_000:2_600_000] = 0
+    d = torch.from_numpy(x).to(eng.device)
+    plan = H.resolve_plan(H.plan_spectrogram(n, 56e6, 2_000_000, 1, True))
+    assert plan.factor == 6
+    dec = eng.decimate(d, plan.factor)
+    assert np.array_equal(dec.cpu().numpy(), x[::plan.factor])
+    f, t, S = vb.create_spectrogram_device(d, 56e6, time_resolution_us=1, engine=eng)
+    strided = eng.stft(d, plan.window, plan.nperseg, plan.noverlap, plan.nfft, plan.fs, scaling="spectrum",
+                       stride=plan.factor)
+    assert torch.equal(S, strided)
+    fr, tr, Sr = O.create_spectrogram(x, 56e6, time_resolution_us=1)
+    assert np.array_equal(f, fr) and np.array_equal(t, tr)
+    assert P.spec_db_error(S.cpu().numpy(), Sr) <= P.SPEC_DB
+
+
+def test_create_spectrogram_engine_error_takes_the_reference_fallback(eng):
+    """utils.py:298 catches every exception of the first attempt.  adaptive_resolution=False with a
+    coarse time resolution asks for nfft > 16384 (above the generic kernel's ceiling): the engine error must lead
+    to the 256/128/512 hann plan like any scipy error does in the reference — never to the caller."""
+    import vector_b200 as vb
+    rng = np.random.default_rng(8)
+    x = (rng.standard_normal(400_000) + 1j * rng.standard_normal(400_000)).astype(np.complex64)
+    f, t, S = vb.create_spectrogram(x, 56e6, time_resolution_us=300, adaptive_resolution=False)
+    import scipy.signal
+    assert S.shape[0] == 512                                # the fallback plan of utils.py:303-313
+    _, tr, Sr = scipy.signal.spectrogram(x, fs=56e6, window="hann", nperseg=256, noverlap=128, nfft=512,
+                                         return_onesided=False, detrend=False, scaling="spectrum")
+    assert np.array_equal(t, tr) and P.spec_db_error(S, np.fft.fftshift(Sr, axes=0)) <= P.SPEC_DB
+
+
+# ------------------------------------------------------------------------------ save path
+def test_streamed_mat_is_byte_identical_to_savemat(eng, tmp_path):
+    """save_vector(CUDA tensor) with more than one 32 MB chunk per plane == scipy.io.savemat after the text header."""
+    from vector_b200 import api
+    n = 9_500_003                                               # 38 MB per plane: two chunks, ragged tail
+    rng = np.random.default_rng(1)
+    v = (rng.standard_normal(n) + 1j * rng.standard_normal(n)).astype(np.complex64)
+    api.save_vector(torch.from_numpy(v).to(eng.device), str(tmp_path / "d.mat"))
+    sio.savemat(str(tmp_path / "s.mat"), {"Y": v, "pre_samples": 0})
+    d, s = (tmp_path / "d.mat").read_bytes(), (tmp_path / "s.mat").read_bytes()
+    assert len(d) == len(s) and d[128:] == s[128:]
+    y, pre = api.load_packet_info(str(tmp_path / "d.mat"))       # the fast reader
+    assert np.array_equal(y, v) and pre == 0 and y.dtype == np.complex64
+    assert api._load_packet_fast(str(tmp_path / "s.mat")) is not None
+
+
+@pytest.mark.parametrize("n", [2, 1000, 9_000_001])
+def test_wv_normalize_branch_matches_mat2wv(eng, tmp_path, n):
+    """save_vector_wv(normalize=True) = mat2wv's bNormalize branch (mat_to_wv_converter.py:30-36): payload
+    bit-exact against the oracle's statement of it, LEVEL OFFS values to 1e-5 dB (the reference's float32 mean
+    is a pairwise float32 sum; ours accumulates in fp64)."""
+    import vector_b200 as vb
+    rng = np.random.default_rng(n)
+    v = (0.3 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))).astype(np.complex64)
+    vb.save_vector_wv(v, str(tmp_path / "g.wv"), 56e6, normalize=True, _date="2026-01-01;00:00:00")
+    O.save_vector_wv(v, str(tmp_path / "o.wv"), 56e6, normalize=True, date="2026-01-01;00:00:00")
+    g, o = (tmp_path / "g.wv").read_bytes(), (tmp_path / "o.wv").read_bytes()
+    hg, ho = g[:g.index(b":#") + 2].decode(), o[:o.index(b":#") + 2].decode()
+    lv = lambda h: [float(x) for x in h.split("{LEVEL OFFS: ")[1].split("}")[0].split(",")]
+    assert hg.split("{LEVEL OFFS")[0] == ho.split("{LEVEL OFFS")[0]
+    assert hg.split("{CLOCK")[1] == ho.split("{CLOCK")[1]
+    assert np.allclose(lv(hg), lv(ho), rtol=0, atol=1e-5)
+    pg = np.frombuffer(g[len(hg):-1], np.int16)
+    po = np.frombuffer(o[len(ho):-1], np.int16)
+    m = np.max(np.abs(v))
+    m_exact = np.float32(np.sqrt(np.max(v.real.astype(np.float64) ** 2 + v.imag.astype(np.float64) ** 2)))
+    if m == m_exact:                                        # numpy's SIMD hypot agrees with the correctly rounded max
+        assert np.array_equal(pg, po)
+    else:
+        assert np.max(np.abs(pg.astype(np.int32) - po.astype(np.int32))) <= 1
+    assert g[-1:] == b"}" and len(pg) == 2 * n
+    vb.save_vector_wv(torch.from_numpy(v).to(eng.device), str(tmp_path / "d.wv"), 56e6, normalize=True,
+                      _date="2026-01-01;00:00:00")
+    assert (tmp_path / "d.wv").read_bytes() == g
+
+
+# ------------------------------------------------------------------------------ detect_packet_bounds corners
+@pytest.mark.parametrize("n,fs", [(10, 56e6), (55, 56e6), (56, 56e6), (57, 56e6), (1, 3e6), (3000, 2.5e9)])
+def test_detect_packet_bounds_degenerate_lengths(eng, n, fs):
+    """Signals shorter than the 1 us window (np.convolve 'same' then returns max(n, window) samples centred on the
+    window) and windows above 1024 samples: same indices as the reference's statement."""
+    import vector_b200 as vb
+    rng = np.random.default_rng(n)
+    sig = (0.01 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))).astype(np.complex64)
+    sig[n // 3: n // 3 + max(1, n // 4)] += 1.0
+    assert tuple(int(v) for v in vb.detect_packet_bounds(sig, fs)) == O.detect_packet_bounds(sig, fs)

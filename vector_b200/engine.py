@@ -346,7 +346,11 @@ class Engine:
         percentile of the positive elements (the floor) and the low / high percentiles, minimum and maximum
         of the dB image — is an order statistic of |S|: all eight ranks come out of ONE selection (two
         full reads of S), the dB image is written once, and the six dB values are the dB of six |S| values."""
-        flat = s.contiguous().view(-1)
+        # order statistics and an elementwise map do not care about the element order: frame-major memory
+        # (the transpose view the fused step hands out) is used as it lies, no 448 MB re-layout
+        transposed = s.dim() == 2 and not s.is_contiguous() and s.t().is_contiguous()
+        base = s.t() if transposed else s.contiguous()
+        flat = base.view(-1)
         n = flat.numel()
         if n == 0:
             return torch.empty_like(s), 0, 0
@@ -360,7 +364,9 @@ class Engine:
         v = self.select_finish(flat, ranks)
         floor_ = H.lerp(v[6], v[7], g0) if n_pos > 0 else 1e-12
         floor_ = max(floor_, 1e-12)
-        db = self.db(flat, floor_).view(s.shape)
+        db = self.db(flat, floor_).view(base.shape)
+        if transposed:
+            db = db.t()
         six = self.db(torch.from_numpy(v[:6].copy()).to(self.device), floor_).cpu().numpy()
         vmin, vmax = H.lerp(six[0], six[1], g1), H.lerp(six[2], six[3], g2)
         vmin, vmax = H.colour_limits(vmin, vmax, six[4], six[5], max_dynamic_range)
