@@ -2,20 +2,24 @@
 """bench.py — headline benchmark of the vector-build hot path (BASELINE.json metric:
 "output GSa/s for 6-pkt 1 s@56 MSa/s vector build + STFT; % HBM peak @1/2/4/8 GPU").
 
-One step = one pass of the hot path over one batch of synthetic input:
-    pass A (max |v|^2 over one common period of the packet trains + head/tail, no stores)
-    -> [all-reduce MAX of one double when N > 1] ->
-    ONE fused kernel: recompute, scale, store complex64 AND the full-rate STFT (hann 1024/512,
-    nfft 1024, 'density', fftshifted float32 [1024, frames] handed out as the transpose view of
-    frame-major memory) — every warp builds, transforms and stores its own frames
-on SURVEY.md §8d cfg2 (6 packets, periods 100/50/20/10/5/2 ms, shifts +2/-3/+1/-8/+6/-12 MHz,
-normalisation on).  At N GPUs the vector is N x 1000 ms long and time-sharded, 56 M samples
-(+ halo) per GPU: per-GPU work is fixed -> "scaling": "weak".  value = all samples / max-over-
-ranks device time; `e2e` is the same work through the host-buffer API with the H2D of the
-packets and the D2H of vector + spectrogram inside the timed region.
+Headline step (value / ms_per_step / roofline / e2e) = one pass of the hot path over one batch of synthetic
+input, ONE kernel launch per GPU:
+    max |v|^2 over one common period of the packet trains + head/tail (no stores) -> grid barrier ->
+    recompute, scale, store complex64 AND the full-rate STFT (hann 1024/512, nfft 1024, 'density', fftshifted
+    float32 [1024, frames] handed out as the transpose view of frame-major memory)
+on SURVEY.md §8d cfg2 (6 packets, periods 100/50/20/10/5/2 ms, shifts +2/-3/+1/-8/+6/-12 MHz, normalisation
+on).  At N GPUs the vector is N x 1000 ms long and time-sharded, 56 M samples (+ halo) per GPU: per-GPU work
+is fixed -> "scaling": "weak".  `e2e` is the same work through the host-buffer API with the H2D of the packets
+and the D2H of vector + spectrogram inside the timed region.
 
-`--impl reference` times the reference's own CPU implementation (numpy/scipy, via the oracle
-port that is pinned bit-exact to it) on rank 0.
+The same JSON line carries the other BASELINE.json configs, each with its own `scaling`:
+    "cfg4"  10 s @ 200 MSa/s (2e9 samples), dense periods, packets resampled on the device (K0), time-sharded
+            over the N ranks — STRONG scaling (total work fixed)
+    "cfg5"  256 scenario vectors (3 packets, 100 ms each), 256/N per GPU, no collective — STRONG scaling
+    "save"  (N = 1) the save path at 56 M samples: .mat and .wv written from the device vs the reference's writers
+
+`--impl reference` times the reference's own CPU implementation (numpy/scipy, via the oracle port that is
+pinned bit-exact to the real reference's outputs, tests/golden) on rank 0.
 """
 from __future__ import annotations
 
@@ -24,6 +28,7 @@ import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -41,12 +46,25 @@ WORKLOAD = ("cfg2+cfg3(full): 6 synthetic packets (tone/chirp/BPSK/noise/multito
             "normalisation, then hann 1024/512 nfft-1024 two-sided density STFT")
 
 
+def config_dict(world):
+    """Identical for both arms: what is measured, not how."""
+    return {"workload": WORKLOAD, "samples_per_gpu": N_PER_GPU, "total_samples": N_PER_GPU * world, "n_gpus": world}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
         with open(p) as fh:
             return float(json.load(fh)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
     return 6650.0, "B200_PROFILING.md fallback (of fallback)"
+
+
+def committed(name):
+    try:
+        with open(os.path.join(ROOT, "profiles", name)) as fh:
+            return json.load(fh)
+    except Exception:
+        return None
 
 
 class ClockSampler:
@@ -93,12 +111,44 @@ def workload(n_gpus):
     return cfgs, packets, N_PER_GPU * n_gpus
 
 
+def bind_to_gpu_numa_node(local):
+    """Pin this rank's host threads (and, by first touch, its pinned staging buffers) to the CPUs next to
+    its GPU: eight ranks allocating 0.9 GB of pinned memory each on one node was the suspect for the e2e
+    fall-off at N > 1.  Returns what was found (recorded in the line)."""
+    info = {"numa_node": None, "cpus": None}
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        base = f"/sys/bus/pci/devices/{bdf}"
+        with open(base + "/numa_node") as fh:
+            info["numa_node"] = int(fh.read().strip())
+        with open(base + "/local_cpulist") as fh:
+            spec = fh.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if cpus and cpus != allowed:
+            os.sched_setaffinity(0, cpus)
+        info["cpus"] = len(cpus) if cpus else len(allowed)
+    except Exception as exc:
+        info["error"] = f"{type(exc).__name__}: {exc}"
+    return info
+
+
 # ----------------------------------------------------------------------------- reference arm
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import ref_port as O
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
     cfgs, packets, _ = workload(1)
     # bounded sample: 1000 ms of vector (the per-GPU share, ~2.5 s of CPU per step); shortened to
     # 200 ms when K+W would push the run past a few minutes
@@ -115,18 +165,229 @@ def run_reference(args):
         step()
     dt = (time.perf_counter() - t0) / args.steps
     val = n / dt / 1e9
-    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "GSa/s", "n_gpus": args.gpus,
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "GSa/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "dtype_note": "complex64 samples, float32 arithmetic; packet phase in fp64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": f"{sample_ms} ms of vector ({n} samples) per step"},
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "dtype_note": "complex64 samples, float32 arithmetic; packet phase in fp64", "data": "synthetic",
+            "config": config_dict(world),
             "cpu_baseline": {"value": val, "unit": "GSa/s", "cores": 1, "kind": "port",
                              "host_cores": os.cpu_count(),
-                             "sample": "oracle port (numpy %s / scipy %s): build_vector + scipy.signal.spectrogram "
-                                       "1024/512 on %d samples per step; numpy ufuncs and pocketfft are single-threaded"
-                                       % (np.__version__, __import__("scipy").__version__, n)},
+                             "pinned": "the port is checked bit for bit against outputs of the REAL reference "
+                                       "(tests/golden/make_golden.py -> tests/test_oracle_golden.py); the reference is "
+                                       "pure Python and cannot travel to the GPU box",
+                             "sample": "%d ms of vector (%d samples) per step: oracle port (numpy %s / scipy %s) build_vector "
+                                       "+ scipy.signal.spectrogram 1024/512; numpy ufuncs and pocketfft are single-threaded"
+                                       % (sample_ms, n, np.__version__, __import__("scipy").__version__)},
             "e2e": {"value": val, "unit": "GSa/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- our arm: the other configs
+def run_cfg4(eng, world, rank, dist, args, peak):
+    """BASELINE.json configs[3]: 10 s @ 200 MSa/s, 6 packets with dense periodic repetition, time-sharded over the
+    ranks (strong scaling).  One fused launch per rank builds max + vector + spectrogram of the head; the steady
+    part of the slab is the bit-exact periodic repetition of its first 12 ms and is placed from the vector itself
+    (dist.build_stft_slab / hostmath.tile_plan).  Checks: windows of the slab equal the plain placement kernel
+    run on the packet bank, bit for bit (this is also the tiled-vs-gathered check); Parseval on a few frames."""
+    import scipy.signal
+    import torch
+    from vector_b200 import dist as vdist, generate, hostmath as H, synth
+    from vector_b200._lib import BUILD_SCALE
+    fs = 200e6
+    n = int(args.cfg4_seconds * fs)
+    cfgs, pk = synth.scenario(synth.CFG4_ROWS, 56e6)
+    for c in cfgs:
+        c["sample_rate"] = 56e6
+    info = generate.prepare_bank(eng, cfgs, pk, fs, resample=True)
+    rows = generate.placement_rows(cfgs, info, n, fs)
+    plan = vdist.plan_slab(n, world, rank, 1024, 512, 1, align=512)
+    n_own, nf = plan.hi - plan.lo, plan.frame_hi - plan.frame_lo
+    vec = torch.empty(n_own, dtype=torch.complex64, device=eng.device)
+    spec = eng.alloc_spectrogram(1024, nf, frame_major=True)
+    tp = H.tile_plan(rows, [i[0] for i in info], n, plan.lo, plan.hi)
+
+    def step(tile="auto"):
+        return vdist.build_stft_slab(eng, rows, plan, True, None, fs=fs, out_vec=vec, out_spec=spec, tile=tile)
+
+    def timed(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = eng.launches
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / reps], dtype=torch.float64, device=eng.device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item(), (eng.launches - l0) // reps
+
+    ms_exact, _ = timed(lambda: step(False), 3) if (tp is not None and not args.quick) else (None, None)
+    ms, launches = timed(step, 5)
+    _, _, m = step()
+    # ---- checks
+    ok = True
+    descs, nd = eng.make_descs(rows)
+    w = 2_000_000
+    offs = {0, max(0, n_own - w)}
+    if tp is not None:
+        offs.update({max(0, tp["x1"] - plan.lo - w // 2), max(0, min(n_own - w, tp["x2"] - plan.lo - w // 2)),
+                     max(0, min(n_own - w, (tp["x1"] + 3 * tp["T"]) - plan.lo))})
+    for off in sorted(offs):
+        lo, hi = plan.lo + off, min(plan.lo + off + w, plan.hi)
+        ref = torch.empty(hi - lo, dtype=torch.complex64, device=eng.device)
+        eng.build_pass(descs, nd, lo, hi, ref, BUILD_SCALE, maxsq=m)
+        ok = ok and torch.equal(ref, vec[off:off + (hi - lo)])
+    wn = torch.from_numpy(scipy.signal.get_window("hann", 1024)).to(eng.device)
+    scale = 1.0 / (fs * float((wn * wn).sum()))
+    for f in (0, nf // 3, nf - 1):
+        seg = vec[f * 512: f * 512 + 1024]
+        if seg.numel() < 1024:
+            continue
+        want = float(((seg.to(torch.complex128) * wn).abs() ** 2).sum()) * 1024 * scale
+        got = float(spec[:, f].double().sum())
+        ok = ok and abs(got - want) <= 1e-5 * max(want, 1e-30)
+    flag = torch.tensor([1 if ok else 0], device=eng.device)
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    bytes_rank = 8 * n_own + 4 * 1024 * nf
+    out = None
+    if rank == 0:
+        n1 = committed("r2_cfg4_n1.json")
+        n1_ms = n1.get("ms_per_step") if n1 and abs(n1.get("seconds", 0) - args.cfg4_seconds) < 1e-9 else None
+        if world == 1:
+            n1_ms = ms
+        out = {"workload": f"cfg4: {args.cfg4_seconds:g} s @ 200 MSa/s, 6 packets resampled 56->200 MSa/s on the device, "
+                           "periods 2.0/1.5/1.0/0.8/0.5/0.4 ms (7.9 overlapping instances per sample), normalised, + full-rate STFT",
+               "scaling": "strong", "n_gpus": world, "total_samples": n, "seconds": args.cfg4_seconds,
+               "instances": [r[2] for r in rows], "ms_per_step": ms, "GSa_per_s": n / ms / 1e6,
+               "per_gpu_alg_GBps": bytes_rank / ms / 1e6, "frac_of_measured_peak": bytes_rank / ms / 1e6 / peak,
+               "launches_per_step": launches,
+               "periodic_tiling": None if tp is None else {"T": tp["T"], "x1": tp["x1"], "x2": tp["x2"]},
+               "ms_per_step_without_tiling": ms_exact,
+               "n1_ms_per_step": n1_ms,
+               "n1_source": "this run" if world == 1 else "profiles/r2_cfg4_n1.json (committed N=1 figure)",
+               "efficiency_vs_n1": (n1_ms / (ms * world)) if n1_ms else None,
+               "max_abs": float(np.sqrt(m.item())), "checks_ok": bool(flag.item())}
+    del vec, spec
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_cfg5(eng, world, rank, dist, args, peak):
+    """BASELINE.json configs[4]: 256 scenario vectors (3 packets, 100 ms @ 56 MSa/s each, shift / period / start
+    swept), 256 / N per GPU, no collective.  A step = shift every distinct (packet, shift) once (one launch) + ONE
+    launch that places, normalises (per vector) and stores this rank's vectors."""
+    import torch
+    from vector_b200 import generate, hostmath as H, synth
+    n = 5_600_000
+    total_vec = args.cfg5_vectors
+    mine = list(range(rank, total_vec, world))
+    bank = synth.bank(FS)
+    scen = [synth.configs(synth.cfg5_rows(v)) for v in mine]
+    packets = {c["file"]: bank[c["kind"]] for cfgs in scen for c in cfgs}
+    vecs, _, counts, maxsq = generate.build_batch_device(scen, n, True, packets=packets, engine=eng)   # host tables + first run
+    # the device part of a step, from prepared host tables: re-shift + build
+    batch = eng._last_batch
+    out_buf = torch.empty((len(mine), (n + 1) // 2 * 2), dtype=torch.complex64, device=eng.device)
+    del vecs
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+
+    def step():
+        ev[0].record()
+        eng.batch_prepare(batch, FS)
+        ev[1].record()
+        eng.batch_build(n, True, out=out_buf, maxsq=maxsq)
+        ev[2].record()
+
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    reps, tp, tb = 5, 0.0, 0.0
+    for _ in range(reps):
+        step()
+        torch.cuda.synchronize()
+        tp += ev[0].elapsed_time(ev[1]) / reps
+        tb += ev[1].elapsed_time(ev[2]) / reps
+    t = torch.tensor([tp + tb, tb, tp], dtype=torch.float64, device=eng.device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    # check: a few vectors against single-vector builds (bit for bit) — full oracle parity is tests/test_gpu_sizes.py
+    ok = True
+    for i in (0, len(mine) // 2, len(mine) - 1):
+        pk = [packets[c["file"]] for c in scen[i]]
+        one, _, cnt, m1 = generate.build_vector_device(scen[i], n, True, packets=pk, engine=eng)
+        ok = ok and cnt == counts[i] and torch.equal(one, out_buf[i, :n]) and m1.item() == maxsq[i].item()
+    flag = torch.tensor([1 if ok else 0], device=eng.device)
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    out = None
+    if rank == 0:
+        ms, ms_b, ms_p = t.tolist()
+        n5 = committed("r2_cfg5_n1.json")
+        n1_ms = ms if world == 1 else (n5 or {}).get("ms_per_step")
+        out = {"workload": "cfg5: %d scenario vectors (3 packets, 100 ms @ 56 MSa/s, shift/period/start from default_rng(5000+v)), "
+                           "each normalised by its own max" % total_vec,
+               "scaling": "strong", "n_gpus": world, "vectors": total_vec, "per_gpu": len(mine), "samples_per_vector": n,
+               "ms_per_step": ms, "build_ms": ms_b, "prepare_ms": ms_p,
+               "vectors_per_s": total_vec / ms * 1e3, "GSa_per_s": total_vec * n / ms / 1e6,
+               "per_gpu_alg_GBps": 8 * n * len(mine) / ms_b / 1e6, "frac": 8 * n * len(mine) / ms_b / 1e6 / peak,
+               "frac_note": "8 B per output sample of this rank's vectors / the build launch's time / measured HBM peak",
+               "launches_per_step": 2, "distinct_shifted_packets": eng._last_batch_jobs,
+               "n1_ms_per_step": n1_ms, "efficiency_vs_n1": (n1_ms / (ms * world)) if n1_ms else None,
+               "checks_ok": bool(flag.item())}
+    del out_buf
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_save(eng, vec, args):
+    """The save path at 56 M samples: save_vector / save_vector_wv from the device
+    (plane split / int16 quantise on the GPU, streamed through a pinned ring while the file is written) vs the
+    reference's writers (scipy.io.savemat / mat2wv via the oracle port) on the same vector in host memory."""
+    import torch
+    from oracle import ref_port as O
+    from vector_b200 import api
+    out = {"samples": int(vec.numel())}
+    with tempfile.TemporaryDirectory(dir=args.save_dir) as td:
+        host = vec.cpu().numpy()
+
+        def best(fn, reps=2):
+            ts = []
+            for _ in range(reps):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                fn()
+                ts.append(time.perf_counter() - t0)
+            return min(ts)
+        api.save_vector(vec[:4096], os.path.join(td, "w.mat"))        # warm the pinned ring
+        out["mat_s"] = best(lambda: api.save_vector(vec, os.path.join(td, "g.mat")))
+        out["wv_s"] = best(lambda: api.save_vector_wv(vec, os.path.join(td, "g.wv"), FS))
+        out["ref_savemat_s"] = best(lambda: O.save_vector(host, os.path.join(td, "r.mat")), 1)
+        out["ref_mat2wv_s"] = best(lambda: O.save_vector_wv(host, os.path.join(td, "r.wv"), FS, date="x"), 1)
+        out["load_fast_s"] = best(lambda: api.load_packet_info(os.path.join(td, "g.mat")))
+        import scipy.io as sio
+        out["ref_loadmat_s"] = best(lambda: sio.loadmat(os.path.join(td, "r.mat"), squeeze_me=True)["Y"].astype(np.complex64), 1)
+        with open(os.path.join(td, "g.mat"), "rb") as a, open(os.path.join(td, "r.mat"), "rb") as b:
+            a.seek(128); b.seek(128)
+            same_mat = a.read() == b.read()
+        with open(os.path.join(td, "g.wv"), "rb") as a, open(os.path.join(td, "r.wv"), "rb") as b:
+            ga, rb = a.read(), b.read()
+            same_wv = ga[ga.index(b":#"):] == rb[rb.index(b":#"):]
+        out["files_identical"] = bool(same_mat and same_wv)
+    out["mat_speedup"] = out["ref_savemat_s"] / out["mat_s"]
+    out["wv_speedup"] = out["ref_mat2wv_s"] / out["wv_s"]
+    out["note"] = ("wall clock incl. the file write to %s; ours starts from the vector in HBM, the reference's from the vector "
+                   "in host memory" % (args.save_dir or tempfile.gettempdir()))
+    return out
 
 
 # ----------------------------------------------------------------------------- our arm
@@ -145,56 +406,39 @@ def run_ours(args):
     os.dup2(2, 1)
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 else {"numa_node": None, "cpus": None}
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # stdout carries exactly one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = get_engine(local)
     cfgs, packets, total = workload(world)
-    reduce_max = vdist.make_max_reducer()
-    peer = None
-    if world > 1 and not args.nccl_max and not args.rows:
-        try:                                   # symmetric 64-byte blocks for the in-kernel MAX exchange over NVLink
-            peer = vdist.PeerMax()
-        except Exception as exc:
-            print(f"[bench] symmetric memory unavailable ({type(exc).__name__}: {exc}); NCCL all-reduce form",
-                  file=sys.stderr)
-            peer = None
-
     info = generate.prepare_bank(eng, cfgs, packets, FS)
     rows = generate.placement_rows(cfgs, info, total, FS)
     plan = vdist.plan_slab(total, world, rank, 1024, 512, 1, align=512)     # slabs cut on hop boundaries
     n_own = plan.hi - plan.lo
     n_frames = plan.frame_hi - plan.frame_lo
+    full_ranges = H.max_eval_ranges(rows, [i[0] for i in info], total)
+    range_samples = int(sum(hi - lo for lo, hi in full_ranges))
+    # normalisation across ranks: see dist.build_stft_slab.  default: every rank evaluates the (short) max ranges itself
+    max_mode = "single"
+    if world > 1:
+        max_mode = "nccl" if args.nccl_max else ("peer" if args.peer_max else
+                                                 ("redundant" if range_samples <= vdist.REDUNDANT_MAX_SAMPLES else "peer"))
+    reduce_max = vdist.make_max_reducer() if max_mode == "nccl" else None
+    peer = None
+    if max_mode == "peer":
+        try:                                   # symmetric 64-byte blocks for the in-kernel MAX exchange over NVLink
+            peer = vdist.PeerMax()
+        except Exception as exc:
+            print(f"[bench] symmetric memory unavailable ({type(exc).__name__}: {exc}); NCCL all-reduce form", file=sys.stderr)
+            max_mode, reduce_max = "nccl", vdist.make_max_reducer()
     vec = torch.empty(n_own, dtype=torch.complex64, device=eng.device)
-    spec = eng.alloc_spectrogram(1024, n_frames, frame_major=not args.rows)   # [1024, frames] view of [frames, 1024] memory
-    descs, nd = eng.make_descs(rows, eng.free_flags(rows, total))   # hint bit for the in-kernel max pass
-    max_ranges = eng.max_ranges(rows, total, world, rank)      # this rank's share of one common period + head/tail
-    from vector_b200._lib import BUILD_MAXONLY, BUILD_SCALE
+    spec = eng.alloc_spectrogram(1024, n_frames, frame_major=True)         # [1024, frames] view of [frames, 1024] memory
+    redundant_max = (1 << 62) if max_mode == "redundant" else -1
 
-    ev = lambda: torch.cuda.Event(enable_timing=True)
-    marks = []
-
-    one_launch = (world == 1 and not args.rows and not args.two_launch) or peer is not None
-
-    def step(record=None):
-        e = [ev() for _ in range(3)] if record is not None else None
-        if one_launch:
-            # single GPU: pass A (max |v|^2 over one common period + head/tail) runs INSIDE the fused kernel
-            if e: e[0].record(); e[1].record()
-            eng.build_stft1024(descs, nd, plan.lo, plan.hi, vec, BUILD_SCALE, plan.frame_lo, n_frames, spec,
-                               window="hann", fs=FS, scaling="density", norm_ranges=max_ranges, peer=peer)
-        else:
-            eng._maxsq.zero_()
-            if e: e[0].record()
-            eng.max_pass(descs, nd, max_ranges)                                    # pass A: max |v|^2, no stores
-            if reduce_max is not None:
-                reduce_max(eng._maxsq)                                              # the one collective: 1 double, MAX
-            if e: e[1].record()
-            eng.build_stft1024(descs, nd, plan.lo, plan.hi, vec, BUILD_SCALE, plan.frame_lo, n_frames, spec,
-                               window="hann", fs=FS, scaling="density")            # place + scale + store + STFT
-        if e:
-            e[2].record()
-            record.append(e)
+    def step():
+        vdist.build_stft_slab(eng, rows, plan, True, reduce_max, fs=FS, out_vec=vec, out_spec=spec, peer=peer,
+                              tile=False, redundant_max=redundant_max)
 
     def barrier():
         if world > 1:
@@ -204,13 +448,11 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
-    # The step is 1 launch at N=1 and memset + 2 launches + 1 all-reduce + 1 launch at N>1: capture it in a
-    # CUDA graph so that the timed loop replays device work back to back (no Python / launch gaps).
-    graph = None
-    launches_per_step = None
-    if not args.no_graph and (world == 1 or peer is not None):   # the NCCL form stays eager (an all-reduce inside a captured step hung on this stack)
+    # The step is 1 launch (+ a 24-byte memset): capture it in a CUDA graph so that the timed loop replays device
+    # work back to back (no Python / launch gaps).  The NCCL form stays eager.
+    graph, launches_per_step = None, None
+    if not args.no_graph and max_mode != "nccl":
         try:
-            l0 = eng.launches
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
@@ -230,14 +472,15 @@ def run_ours(args):
             graph = None
             torch.cuda.synchronize()
     barrier()
-    # Clocks: the timed region is a few milliseconds, far below nvidia-smi's sampling period, so the SAME step
-    # keeps the GPU busy for ~0.5 s before it and ~0.3 s after it (fixed iteration counts: identical on every
-    # rank) while rank 0 samples clocks and throttle reasons every 100 ms.
+
     def run_one():
         if graph is not None:
             graph.replay()
         else:
             step()
+    # Clocks: the timed region is a few milliseconds, far below nvidia-smi's sampling period, so the SAME step
+    # keeps the GPU busy for ~0.5 s before it and ~0.3 s after it (fixed iteration counts: identical on every
+    # rank) while rank 0 samples clocks and throttle reasons every 100 ms.
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -246,13 +489,10 @@ def run_ours(args):
         run_one()
     barrier()
     launches0 = eng.launches
-    t_start, t_end = ev(), ev()
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_start.record()
     for _ in range(args.steps):
-        if graph is not None:
-            graph.replay()
-        else:
-            step(marks)
+        run_one()
     t_end.record()
     barrier()
     ms_total = t_start.elapsed_time(t_end)
@@ -260,10 +500,6 @@ def run_ours(args):
         run_one()
     barrier()
     launches = launches_per_step * args.steps if graph is not None else eng.launches - launches0
-    if graph is not None:                                          # per-kernel split: a few eager steps after the timed region
-        for _ in range(min(args.steps, 10)):
-            step(marks)
-        barrier()
     clocks = sampler.stop() if rank == 0 else None
     if clocks is not None:
         clocks["window"] = (f"{args.load_steps} untimed steps before + the timed region + {args.load_steps * 3 // 5} after, "
@@ -272,29 +508,23 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
     ms_step = ms_t.item() / args.steps
-    k_ms = np.array([[m[i].elapsed_time(m[i + 1]) for i in range(2)] for m in marks]).mean(axis=0)
-    k_src = "CUDA events around each launch in the timed loop"
-    if graph is not None and one_launch:
-        # the step IS one launch of the dominant kernel: its average duration over the timed region is the
-        # event-timed region / K (launch gaps included, so this is the conservative figure)
-        k_ms = np.array([0.0, ms_step])
-        k_src = "timed region / K: the step is exactly one launch of this kernel (CUDA graph replay)"
+    peer_status = eng.peer_status() if peer is not None else 0
 
     # ---- e2e through the host-buffer API: H2D packets, D2H vector + spectrogram, every step
     pinned_pk = [(torch.from_numpy(np.ascontiguousarray(y)).pin_memory(), pre) for y, pre in packets]
     out_vec = torch.empty(n_own, dtype=torch.complex64).pin_memory()
-    spec_mem = spec.t() if spec.stride(0) == 1 else spec               # the contiguous side of the buffer
+    spec_mem = spec.t()                                                     # the contiguous side of the buffer
     out_spec = torch.empty(spec_mem.shape, dtype=torch.float32).pin_memory()
 
     def e2e_step():
         pk = [(t.numpy(), pre) for t, pre in pinned_pk]
         generate.prepare_bank(eng, cfgs, pk, FS)                          # H2D of every packet + shift
-        v, s, _ = vdist.build_stft_slab(eng, rows, plan, True, reduce_max if peer is None else None, fs=FS,
-                                        out_vec=vec, out_spec=spec, peer=peer)
+        v, s, _ = vdist.build_stft_slab(eng, rows, plan, True, reduce_max, fs=FS, out_vec=vec, out_spec=spec,
+                                        peer=peer, tile=False, redundant_max=redundant_max)
         out_vec.copy_(v, non_blocking=True)
-        out_spec.copy_(s.t() if s.stride(0) == 1 else s, non_blocking=True)
+        out_spec.copy_(s.t(), non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        return float(out_spec.flatten()[512]) + float(out_vec[0].real)   # read the result on the host
+        return float(out_spec[0, 512]) + float(out_vec[0].real)          # read the result on the host
 
     e2e_steps = max(2, min(args.steps, 5))
     e2e_step()
@@ -304,65 +534,97 @@ def run_ours(args):
         e2e_step()
     barrier()
     e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3 / e2e_steps], dtype=torch.float64, device=eng.device)
+    # raw pinned D2H of the same two buffers, all ranks at once: the platform's ceiling for the e2e step
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        out_vec.copy_(vec, non_blocking=True)
+        out_spec.copy_(spec_mem, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    barrier()
+    d2h_ms = torch.tensor([(time.perf_counter() - t0) * 1e3 / 3], dtype=torch.float64, device=eng.device)
     if world > 1:
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(d2h_ms, op=dist.ReduceOp.MAX)
     h2d = sum(t.numel() * 8 for t, _ in pinned_pk)
     d2h = out_vec.numel() * 8 + out_spec.numel() * 4
+    numa_all = [numa]
+    if world > 1:
+        numa_all = [None] * world
+        dist.all_gather_object(numa_all, numa)
+
+    peak, peak_src = peaks()
+    save = None
+    if world == 1 and not args.no_save and not args.quick:
+        try:
+            save = run_save(eng, vec, args)
+        except Exception as exc:
+            save = {"error": f"{type(exc).__name__}: {exc}"}
+    del out_vec, out_spec, spec_mem
+    fused_bytes = 8 * n_own + 4 * spec.numel()
+    del vec, spec
+    torch.cuda.empty_cache()
+    cfg4 = cfg5 = None
+    if not args.no_cfg4:
+        try:
+            cfg4 = run_cfg4(eng, world, rank, dist, args, peak)
+        except Exception as exc:
+            cfg4 = {"error": f"{type(exc).__name__}: {exc}"}
+            torch.cuda.empty_cache()
+    if not args.no_cfg5:
+        try:
+            cfg5 = run_cfg5(eng, world, rank, dist, args, peak)
+        except Exception as exc:
+            cfg5 = {"error": f"{type(exc).__name__}: {exc}"}
 
     if rank == 0:
-        peak, peak_src = peaks()
-        fused_bytes = 8 * n_own + 4 * spec.numel()
-        kernels = {
-            "place_max(passA)": {"ms": k_ms[0], "alg_bytes": 0, "in_fused_kernel": bool(one_launch),
-                                 "samples_evaluated": int(sum(hi - lo for lo, hi in max_ranges)),
-                                 "note": "no HBM output; L2-resident bank reads only; the periodic packet trains repeat "
-                                         "bit-exactly, so one common period + head/tail of the vector gives the exact max" + (
-                                     "; includes the 1-double all-reduce" if world > 1 else "")},
-            "build_stft1024(fused passB+STFT)": {"ms": k_ms[1], "alg_bytes": fused_bytes,
-                                                 "note": "8 B/Sa vector store + 8 B/Sa spectrogram store, nothing read" + (
-                                                     "; includes pass A (max over one common period + head/tail) and its grid barrier" if one_launch else "")},
-        }
-        for k in kernels.values():
-            k["GBps"] = k["alg_bytes"] / (k["ms"] * 1e-3) / 1e9 if k["ms"] > 0 else None
         traffic = None
-        try:                                                   # per-launch DRAM bytes of the dominant kernel, from the committed ncu capture
-            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
-                t = json.load(fh)["wf1024_kernel"]
-            if not args.rows and world == 1:
-                traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
-        except Exception:
-            traffic = None
-        dom = "build_stft1024(fused passB+STFT)"
-        kname = "tile1024_kernel<1,16,0> (C-order rows)" if args.rows else "wf1024_kernel (warp per frame, frame-major memory)"
-        ach = kernels[dom]["GBps"]
+        t = committed("ncu_traffic.json")
+        if t and world == 1:
+            try:
+                traffic = t["wf1024_kernel"]["dram_bytes_read"] + t["wf1024_kernel"]["dram_bytes_write"]
+            except Exception:
+                traffic = None
+        ach = fused_bytes / (ms_step * 1e-3) / 1e9
+        par = {"single": "single GPU: max pass, grid barrier, build + STFT in ONE launch",
+               "redundant": f"time-slab x{world}, ONE launch per GPU, no collective: the ranges that hold the global max (one common "
+                            f"period of the packet trains + head/tail, {range_samples} samples) are evaluated by every rank inside its launch",
+               "peer": f"time-slab x{world}, ONE launch per GPU: MAX of one double exchanged inside the kernel over NVLink peer memory "
+                       "(system-scope atomics, torch symmetric memory)",
+               "nccl": f"time-slab x{world}, pass A launch + 1 scalar NCCL all-reduce(MAX) + fused launch"}[max_mode]
         line = {
             "metric": METRIC, "value": total / (ms_step * 1e-3) / 1e9, "unit": "GSa/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "dtype_note": "complex64 samples, float32 arithmetic; packet phase in fp64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "samples_per_gpu": N_PER_GPU, "total_samples": total,
-                       "parallelism": (f"time-slab x{world}, ONE launch per GPU: MAX of one double exchanged inside the kernel over "
-                                       f"NVLink peer memory (system-scope atomics, torch symmetric memory)" if peer is not None else
-                                       f"time-slab x{world}, pass A launch + 1 scalar NCCL all-reduce(MAX) + fused launch")
-                       if world > 1 else "single GPU",
-                       "l2": "no flush: each step writes 896 MB per GPU (vector + spectrogram), far above the 126 MB L2",
-                       "timed_loop": "CUDA graph replay of one step, K times" if graph is not None else "eager launches"},
-            "roofline": {"bound": "hbm", "kernel": dom, "cuda_kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s",
+            "config": config_dict(world),
+            "run": {"parallelism": par, "max_mode": max_mode, "peer_status": peer_status,
+                    "l2": "no flush: each step writes 896 MB per GPU (vector + spectrogram), far above the 126 MB L2",
+                    "timed_loop": "CUDA graph replay of one step, K times" if graph is not None else "eager launches",
+                    "numa": numa_all},
+            "roofline": {"bound": "hbm", "kernel": "build_stft1024(fused max + build + STFT)",
+                         "cuda_kernel": "wf1024_kernel<4,0,true,false> (warp per frame, frame-major memory)",
+                         "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "frac_of_nominal_8000": ach / 8000.0, "traffic": traffic,
                          "traffic_source": "profiles/ncu_traffic.json (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)" if traffic else None,
-                         "alg_bytes_per_launch": fused_bytes,
-                         "peak_source": peak_src, "kernel_time_source": k_src,
-                         "step_frac": fused_bytes / (ms_step * 1e-3) / 1e9 / peak},
-            "kernels": kernels,
+                         "alg_bytes_per_launch": fused_bytes, "peak_source": peak_src,
+                         "kernel_time_source": "timed region / K: the step is exactly one launch of this kernel (CUDA graph replay; the "
+                                               "24-byte counter memset ahead of it included)" if graph is not None else
+                                               "timed region / K (eager launches)",
+                         "samples_in_max_pass": range_samples},
             "e2e": {"value": total / (e2e_ms.item() * 1e-3) / 1e9, "unit": "GSa/s", "ms_per_step": e2e_ms.item(),
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                    "api": "generate.prepare_bank + dist.build_stft_slab, pinned host buffers"},
+                    "api": "generate.prepare_bank + dist.build_stft_slab, pinned host buffers",
+                    "raw_d2h_ms": d2h_ms.item(), "raw_d2h_GBps_per_gpu": d2h / d2h_ms.item() / 1e6,
+                    "raw_d2h_note": "the same two pinned copies alone, all ranks at once: the platform's PCIe / host-memory ceiling for this step"},
             "gpu_launches": launches, "clocks": clocks,
+            "cfg4": cfg4, "cfg5": cfg5, "save": save,
         }
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line), file=json_out, flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
@@ -383,6 +645,7 @@ def cpu_baseline():
             best, parts = t2 - t0, (t1 - t0, t2 - t1)
     return {"value": N_PER_GPU / best / 1e9, "unit": "GSa/s", "cores": 1, "host_cores": os.cpu_count(),
             "kind": "port", "build_s": parts[0], "stft_s": parts[1],
+            "pinned": "port checked bit for bit against outputs of the real reference (tests/golden)",
             "sample": "full cfg2 workload once (56 M samples): oracle build_vector + scipy.signal.spectrogram 1024/512, "
                       "best of 2; numpy %s scipy %s, single-threaded like the reference" % (
                           np.__version__, __import__("scipy").__version__)}
@@ -398,13 +661,18 @@ def main():
     ap.add_argument("--load-steps", type=int, default=2500,
                     help="untimed steps run around the timed region so that nvidia-smi can sample clocks under load")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replays")
+    ap.add_argument("--peer-max", action="store_true",
+                    help="A/B at N>1: each rank evaluates its SHARE of the max ranges and the maxima are MAX-combined inside the "
+                         "kernel over NVLink peer memory (default when the ranges are long; short ranges are evaluated by every rank)")
     ap.add_argument("--nccl-max", action="store_true",
-                    help="A/B at N>1: pass A launch + NCCL all-reduce(MAX) + fused launch instead of the in-kernel peer-memory MAX")
-    ap.add_argument("--two-launch", action="store_true",
-                    help="A/B at N=1: pass A as its own launch (the multi-GPU form) instead of inside the fused kernel")
-    ap.add_argument("--rows", action="store_true",
-                    help="A/B: C-order [1024, frames] spectrogram memory (16-frame tile kernel) instead of "
-                         "frame-major memory (warp-per-frame kernel)")
+                    help="A/B at N>1: pass A launch + NCCL all-reduce(MAX) + fused launch")
+    ap.add_argument("--no-cfg4", action="store_true")
+    ap.add_argument("--no-cfg5", action="store_true")
+    ap.add_argument("--no-save", action="store_true")
+    ap.add_argument("--quick", action="store_true", help="skip the save record and the cfg4 no-tiling A/B")
+    ap.add_argument("--cfg4-seconds", type=float, default=10.0)
+    ap.add_argument("--cfg5-vectors", type=int, default=256)
+    ap.add_argument("--save-dir", default=None, help="directory for the save record's temporary files")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

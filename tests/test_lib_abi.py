@@ -30,7 +30,8 @@ def test_every_declared_symbol_is_exported(lib):
 
 
 def test_struct_layout_matches_header():
-    from vector_b200._lib import PktDesc
+    from vector_b200._lib import BatchPkt, PktDesc
+    assert C.sizeof(BatchPkt) == 40 and BatchPkt.freq_hz.offset == 32 and BatchPkt.src_slot.offset == 24
     assert C.sizeof(PktDesc) == 32
     assert (PktDesc.start.offset, PktDesc.period.offset, PktDesc.count.offset, PktDesc.slot.offset) == (0, 8, 16, 24)
 

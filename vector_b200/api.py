@@ -463,7 +463,7 @@ def detect_packet_bounds(signal, sample_rate, threshold_ratio=0.2):
     n = dev.numel()
     window = max(1, int(sample_rate // 1_000_000))
     if n == 0:
-        raise ValueError("zero-size array to reduction operation maximum which has no identity")   # smoothed.max()
+        raise ValueError("v cannot be empty")                  # np.convolve on an empty signal, utils.py:816
     if window > 4096:
         raise ValueError(f"detect_packet_bounds: smoothing window of {window} samples (sample rate above 4 GHz)")
     if n < window:

@@ -157,6 +157,10 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
                  sum(hi - lo for lo, hi in full_ranges) <= redundant_max)
     in_kernel_max = normalize and frame_major and (redundant or peer is not None or
                                                    (plan.world == 1 and reduce_max is None))
+    if normalize and plan.world > 1 and not redundant and peer is None and reduce_max is None:
+        raise ValueError("a sharded normalised build needs a way to combine the per-rank maxima: pass `peer` "
+                         "(in-kernel exchange), `reduce_max` (all-reduce), or let every rank evaluate the max "
+                         "ranges itself (redundant_max)")
     descs, nd = engine.make_descs(rows, engine.free_flags(rows, plan.total) if in_kernel_max else None)
 
     tp = None

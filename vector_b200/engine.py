@@ -401,6 +401,8 @@ class Engine:
         check(self.lib.b200vec_batch_prepare(self._ctx, pk, first, len(scenarios), float(fs_hz), self._stream()))
         self.launches += 1
         self._batch_n = len(scenarios)
+        self._last_batch = scenarios
+        self._last_batch_jobs = len({(int(r[3]), float(r[4])) for sc in scenarios for r in sc})
 
     def batch_build(self, total, normalize=True, out=None, maxsq=None):
         """All vectors of the prepared batch in ONE launch (b200vec_batch_build): returns
