@@ -1,8 +1,8 @@
 #!/bin/bash
+# One GPU-box visit: smoke, parity tests, bench.  Everything lands in gpurun_out/.
 mkdir -p gpurun_out
-P=$PWD/vector_b200/csrc
-for i in 1 2; do
-B200VEC_LIB=$P/libb200vec.so timeout 100 python scripts/norm_ab.py "" 2>&1 | head -1
-B200VEC_LIB=$P/libb200vec_pd.so timeout 100 python scripts/norm_ab.py "" 2>&1 | head -1
-done
-B200VEC_LIB=$P/libb200vec_pd.so timeout 200 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "fused" 2>&1 | tail -2
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
+python -c "import __graft_entry__ as g; g.build(); g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
+timeout ${PYTEST_TIMEOUT:-1500} python -m pytest tests -m gpu -q -rf --timeout 900 ${PYTEST_ARGS} > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" >> gpurun_out/bench.err
+tail -5 gpurun_out/smoke.log; tail -40 gpurun_out/pytest_gpu.log; cat gpurun_out/bench.json; tail -8 gpurun_out/bench.err
