@@ -182,7 +182,7 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
     # ---- launch 1: [lo, x1) from the packet bank, with the normalisation
     mode, norm_ranges, use_peer = BUILD_STORE, None, None
     if in_kernel_max:
-        if redundant or plan.world == 1:
+        if redundant or (plan.world == 1 and peer is None):
             norm_ranges = full_ranges
         else:
             norm_ranges = H.split_ranges(full_ranges, plan.world, plan.rank)
