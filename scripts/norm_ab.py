@@ -43,7 +43,8 @@ def timeit(label, env):
         g.replay()
     b.record(); b.synchronize()
     us = a.elapsed_time(b) / reps * 1e3
-    print(f"{label:50s} {us:7.1f} us/step -> {(8*N + 4*1024*nf)/us/1e3:6.0f} GB/s  maxsq {m.item():.9g}", flush=True)
+    ck = (int(vec.view(torch.int32).sum(dtype=torch.int64).item()), int(spec.view(torch.int32).sum(dtype=torch.int64).item()))
+    print(f"{label:50s} {us:7.1f} us/step -> {(8*N + 4*1024*nf)/us/1e3:6.0f} GB/s  maxsq {m.item():.9g}  checksums {ck[0]} {ck[1]}  lib {os.environ.get('B200VEC_LIB', 'default')}", flush=True)
     return vec.clone(), spec.clone()
 
 

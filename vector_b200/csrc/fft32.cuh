@@ -7,10 +7,15 @@
 // register array whose indices are all compile-time constants: the bit-reversed input order is
 // a renaming of registers, not a permutation.
 //
-// Instruction economy (the STFT kernel is FP32-issue-bound, profiles/README.md):
-//   * a DIT butterfly  (a, b) -> (a + w b, a - w b)  is 6 FMA-pipe instructions:
-//         y0 = a + w b   as two chained FMAs per component,   y1 = 2 a - y0   as one FMA
-//     (4 when w is 1 or -i);
+// Instruction economy (the STFT kernel is FP32-issue-bound, profiles/README.md).  sm_100a has packed
+// FP32 instructions (FFMA2 / FADD2 / FMUL2: one issue slot, two IEEE fp32 results) whose operands take
+// a half swap and per-half signs for free (R.F32x2.LO_HI.NP in SASS), so a complex number kept as one
+// (re, im) register pair costs ONE instruction per complex add, scale or "+ s * (-i b)" term.  All
+// arithmetic below goes through the c_* helpers: packed on the device, the same IEEE operations in the
+// same order as scalar code on the host (tests/test_fft_core.py) — bit-identical results either way.
+//   * a DIT butterfly  (a, b) -> (a + w b, a - w b)  is 3 packed instructions (6 scalar):
+//         u = a + s (-i b),  y0 = u + c b   (two chained FMAs),   y1 = 2 a - y0   (one FMA)
+//     (2 when w is 1 or -i);
 //   * the window multiply is folded into the first stage of the first transform
 //         y0 = wa*a + wb*b,  y1 = wa*a - wb*b        (2 FMUL + 4 FFMA instead of 4 FMUL + 4 FADD)
 //   * the W1024^(l q) twiddles are folded into the first stage of the second transform
@@ -30,9 +35,49 @@
 
 namespace b200vec {
 
-struct cf32 {
+struct alignas(8) cf32 {
     float x, y;
 };
+
+// ---- packed complex helpers.  Every function is one FFMA2 / FADD2 / FMUL2 on the device.
+#ifdef __CUDA_ARCH__
+#define B2_P2(v) make_float2((v).x, (v).y)
+B2_HD cf32 b2_from2(float2 r) { return cf32{r.x, r.y}; }
+// a + b, a - b
+B2_HD cf32 c_add(cf32 a, cf32 b) { return b2_from2(__fadd2_rn(B2_P2(a), B2_P2(b))); }
+B2_HD cf32 c_sub(cf32 a, cf32 b) { return b2_from2(__fadd2_rn(B2_P2(a), make_float2(-b.x, -b.y))); }
+// a + (-i b) = a + (b.y, -b.x);   a - (-i b)
+B2_HD cf32 c_add_mi(cf32 a, cf32 b) { return b2_from2(__fadd2_rn(B2_P2(a), make_float2(b.y, -b.x))); }
+B2_HD cf32 c_sub_mi(cf32 a, cf32 b) { return b2_from2(__fadd2_rn(B2_P2(a), make_float2(-b.y, b.x))); }
+// s * a (real scalar)
+B2_HD cf32 c_scale(cf32 a, float s) { return b2_from2(__fmul2_rn(B2_P2(a), make_float2(s, s))); }
+// s * b + c,  -s * b + c
+B2_HD cf32 c_fma(cf32 b, float s, cf32 c) { return b2_from2(__ffma2_rn(B2_P2(b), make_float2(s, s), B2_P2(c))); }
+B2_HD cf32 c_fnma(cf32 b, float s, cf32 c) { return b2_from2(__ffma2_rn(make_float2(-b.x, -b.y), make_float2(s, s), B2_P2(c))); }
+// s * (-i b) + c = (s b.y + c.x, -s b.x + c.y);   s * (i b) + c = (-s b.y + c.x, s b.x + c.y)
+B2_HD cf32 c_fma_mi(cf32 b, float s, cf32 c) { return b2_from2(__ffma2_rn(make_float2(b.y, -b.x), make_float2(s, s), B2_P2(c))); }
+B2_HD cf32 c_fma_pi(cf32 b, float s, cf32 c) { return b2_from2(__ffma2_rn(make_float2(-b.y, b.x), make_float2(s, s), B2_P2(c))); }
+// s * (i b)  (no addend)
+B2_HD cf32 c_scale_pi(cf32 b, float s) { return b2_from2(__fmul2_rn(make_float2(-b.y, b.x), make_float2(s, s))); }
+// 2 a - y
+B2_HD cf32 c_2a_minus(cf32 a, cf32 y) { return b2_from2(__ffma2_rn(B2_P2(a), make_float2(2.0f, 2.0f), make_float2(-y.x, -y.y))); }
+#undef B2_P2
+#else
+B2_HD cf32 c_add(cf32 a, cf32 b) { return cf32{a.x + b.x, a.y + b.y}; }
+B2_HD cf32 c_sub(cf32 a, cf32 b) { return cf32{a.x - b.x, a.y - b.y}; }
+B2_HD cf32 c_add_mi(cf32 a, cf32 b) { return cf32{a.x + b.y, a.y - b.x}; }
+B2_HD cf32 c_sub_mi(cf32 a, cf32 b) { return cf32{a.x - b.y, a.y + b.x}; }
+B2_HD cf32 c_scale(cf32 a, float s) { return cf32{a.x * s, a.y * s}; }
+B2_HD cf32 c_fma(cf32 b, float s, cf32 c) { return cf32{fmaf(b.x, s, c.x), fmaf(b.y, s, c.y)}; }
+B2_HD cf32 c_fnma(cf32 b, float s, cf32 c) { return cf32{fmaf(-b.x, s, c.x), fmaf(-b.y, s, c.y)}; }
+B2_HD cf32 c_fma_mi(cf32 b, float s, cf32 c) { return cf32{fmaf(b.y, s, c.x), fmaf(-b.x, s, c.y)}; }
+B2_HD cf32 c_fma_pi(cf32 b, float s, cf32 c) { return cf32{fmaf(-b.y, s, c.x), fmaf(b.x, s, c.y)}; }
+B2_HD cf32 c_scale_pi(cf32 b, float s) { return cf32{-b.y * s, b.x * s}; }
+B2_HD cf32 c_2a_minus(cf32 a, cf32 y) { return cf32{fmaf(2.0f, a.x, -y.x), fmaf(2.0f, a.y, -y.y)}; }
+#endif
+// t a  and  u + t b  for a twiddle t held as two scalars: t a = t.x a + t.y (i a), two instructions each
+B2_HD cf32 c_twmul(cf32 a, cf32 t) { return c_fma_pi(a, t.y, c_scale(a, t.x)); }
+B2_HD cf32 c_twmul_add(cf32 b, cf32 t, cf32 u) { return c_fma(b, t.x, c_fma_pi(b, t.y, u)); }
 
 B2_HD float b2_fma(float a, float b, float c) {
 #ifdef __CUDA_ARCH__
@@ -75,20 +120,18 @@ template <int K>
 B2_HD void dit_bfly(cf32 &a, cf32 &b) {
     if constexpr (K == 0) {
         const cf32 t = b;
-        b.x = a.x - t.x; b.y = a.y - t.y;
-        a.x = a.x + t.x; a.y = a.y + t.y;
+        b = c_sub(a, t);
+        a = c_add(a, t);
     } else if constexpr (K == 8) {          // w = -i : w b = (b.y, -b.x)
         const cf32 t = b;
-        b.x = a.x - t.y; b.y = a.y + t.x;
-        a.x = a.x + t.y; a.y = a.y - t.x;
+        b = c_sub_mi(a, t);
+        a = c_add_mi(a, t);
     } else {
         constexpr float c = W32c<K>::v, s = W32s<K>::v;
-        // w b = (b.x c + b.y s,  b.y c - b.x s)
-        const float y0x = b2_fma(b.x, c, b2_fma(b.y, s, a.x));
-        const float y0y = b2_fma(b.y, c, b2_fma(-b.x, s, a.y));
-        b.x = b2_fma(2.0f, a.x, -y0x);
-        b.y = b2_fma(2.0f, a.y, -y0y);
-        a.x = y0x; a.y = y0y;
+        // w b = c b + s (-i b) = (b.x c + b.y s,  b.y c - b.x s)
+        const cf32 y0 = c_fma(b, c, c_fma_mi(b, s, a));
+        b = c_2a_minus(a, y0);
+        a = y0;
     }
 }
 
@@ -120,10 +163,10 @@ template <int P>
 B2_HD void win_bfly(cf32 (&v)[32], const float (&win)[32]) {
     constexpr int i = 2 * P;
     const float wa = win[brev5(i)], wb = win[brev5(i + 1)];
-    const float ux = wa * v[i].x, uy = wa * v[i].y;
+    const cf32 u = c_scale(v[i], wa);
     const cf32 b = v[i + 1];
-    v[i].x = b2_fma(wb, b.x, ux);     v[i].y = b2_fma(wb, b.y, uy);
-    v[i + 1].x = b2_fma(-wb, b.x, ux); v[i + 1].y = b2_fma(-wb, b.y, uy);
+    v[i] = c_fma(b, wb, u);
+    v[i + 1] = c_fnma(b, wb, u);
 }
 B2_HD void fft32_windowed(cf32 (&v)[32], const float (&win)[32]) {
     win_bfly<0>(v, win); win_bfly<1>(v, win); win_bfly<2>(v, win); win_bfly<3>(v, win);
@@ -141,10 +184,10 @@ struct f32x4 {
 template <int P>
 B2_HD void win_bfly2(cf32 (&v)[32], const float wa, const float wb) {
     constexpr int i = 2 * P;
-    const float ux = wa * v[i].x, uy = wa * v[i].y;
+    const cf32 u = c_scale(v[i], wa);
     const cf32 b = v[i + 1];
-    v[i].x = b2_fma(wb, b.x, ux);     v[i].y = b2_fma(wb, b.y, uy);
-    v[i + 1].x = b2_fma(-wb, b.x, ux); v[i + 1].y = b2_fma(-wb, b.y, uy);
+    v[i] = c_fma(b, wb, u);
+    v[i + 1] = c_fnma(b, wb, u);
 }
 template <int K, class W4>
 B2_HD void win_quad(cf32 (&v)[32], const W4 &w4) {
@@ -170,16 +213,12 @@ B2_HD void tw_bfly(cf32 (&v)[32], const TW &tw) {
         u = v[i];
     } else {
         const cf32 ta = tw(la);
-        u.x = b2_fma(-v[i].y, ta.y, v[i].x * ta.x);
-        u.y = b2_fma(v[i].y, ta.x, v[i].x * ta.y);
+        u = c_twmul(v[i], ta);
     }
     const cf32 tb = tw(lb);
-    const cf32 b = v[i + 1];
-    const float y0x = b2_fma(b.x, tb.x, b2_fma(-b.y, tb.y, u.x));
-    const float y0y = b2_fma(b.x, tb.y, b2_fma(b.y, tb.x, u.y));
-    v[i + 1].x = b2_fma(2.0f, u.x, -y0x);
-    v[i + 1].y = b2_fma(2.0f, u.y, -y0y);
-    v[i].x = y0x; v[i].y = y0y;
+    const cf32 y0 = c_twmul_add(v[i + 1], tb, u);
+    v[i + 1] = c_2a_minus(u, y0);
+    v[i] = y0;
 }
 template <class TW>
 B2_HD void fft32_twiddled(cf32 (&v)[32], const TW &tw) {
@@ -204,15 +243,11 @@ B2_HD void tw2_bfly(cf32 (&v)[32], const TW2 &tw2) {
     if constexpr (P == 0) {                     // la = 0: twiddle 1
         u = v[i];
     } else {
-        u.x = b2_fma(-v[i].y, t.ay, v[i].x * t.ax);
-        u.y = b2_fma(v[i].y, t.ax, v[i].x * t.ay);
+        u = c_twmul(v[i], cf32{t.ax, t.ay});
     }
-    const cf32 b = v[i + 1];
-    const float y0x = b2_fma(b.x, t.bx, b2_fma(-b.y, t.by, u.x));
-    const float y0y = b2_fma(b.x, t.by, b2_fma(b.y, t.bx, u.y));
-    v[i + 1].x = b2_fma(2.0f, u.x, -y0x);
-    v[i + 1].y = b2_fma(2.0f, u.y, -y0y);
-    v[i].x = y0x; v[i].y = y0y;
+    const cf32 y0 = c_twmul_add(v[i + 1], cf32{t.bx, t.by}, u);
+    v[i + 1] = c_2a_minus(u, y0);
+    v[i] = y0;
 }
 template <class TW2>
 B2_HD void fft32_twiddled_pairs(cf32 (&v)[32], const TW2 &tw2) {

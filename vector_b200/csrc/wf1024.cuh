@@ -172,7 +172,7 @@ __device__ __forceinline__ bool wf_build_half(const WfArgs &a, unsigned active, 
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                     const float2 v = wf_ldg_keep(base + 32 * j, keep);
-                    x[j].x += v.x; x[j].y += v.y;
+                    x[j] = __fadd2_rn(x[j], v);              // FADD2: one issue slot per complex add
                 }
             } else {
 #pragma unroll
@@ -180,7 +180,7 @@ __device__ __forceinline__ bool wf_build_half(const WfArgs &a, unsigned active, 
                     const int n = r + lane + 32 * j;
                     if (n >= 0 && n < len) {
                         const float2 v = wf_ldg_keep(base + 32 * j, keep);
-                        x[j].x += v.x; x[j].y += v.y;
+                        x[j] = __fadd2_rn(x[j], v);
                     }
                 }
             }
@@ -219,7 +219,7 @@ __device__ __forceinline__ void wf_store_half(float2 *vec, long long s, long lon
                                               unsigned long long pol) {
     if (live) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) { x[j].x *= scl; x[j].y *= scl; }
+        for (int j = 0; j < 16; ++j) x[j] = __fmul2_rn(x[j], make_float2(scl, scl));
     }
     if (!STORE || s >= n_vec) return;
     float2 *dst = vec + s;
