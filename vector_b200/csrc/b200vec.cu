@@ -298,6 +298,38 @@ static int fill_place_args(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int 
     return 0;
 }
 
+// Max-pass planner (maxspans.cuh): the must-evaluate spans of `ranges` for the packets of `pa`, uploaded into the
+// context's cache (reused while descriptors and ranges do not change — every replay of a captured step, every
+// repeated step of one scenario).
+static int upload_spans(SpanCache &c, unsigned long long key, const std::vector<MaxSpan> &spans, cudaStream_t st) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    B2_CUDA(cudaStreamIsCapturing(st, &cs));
+    B2_REQUIRE(cs == cudaStreamCaptureStatusNone,
+               "the max-span list of this (descriptors, ranges) pair is not uploaded yet: run the step once before capturing it in a CUDA graph");
+    if (ensure_scratch(c.dev, (spans.size() + 1) * sizeof(MaxSpan))) return 1;
+    c.n = -1;
+    if (!spans.empty())          // pageable source: the call returns once the data is staged
+        B2_CUDA(cudaMemcpyAsync(c.dev.ptr, spans.data(), spans.size() * sizeof(MaxSpan), cudaMemcpyHostToDevice, st));
+    c.key = key; c.n = (long long)spans.size();
+    return 0;
+}
+
+static int plan_max_spans(b200vec_ctx *ctx, const PlaceArgs &pa, const long long *ranges, int n_ranges,
+                          cudaStream_t st, const MaxSpan **spans_dev, long long *n_spans) {
+    MaxSpanPacket pk[B200VEC_MAX_PACKETS];
+    for (int p = 0; p < pa.np; ++p)
+        pk[p] = MaxSpanPacket{pa.d[p].start, pa.d[p].period, pa.d[p].count, (long long)pa.d[p].len, pa.d[p].free_inst};
+    const unsigned long long key = max_spans_key(pk, pa.np, ranges, n_ranges);
+    SpanCache &c = ctx->max_spans;
+    if (c.n < 0 || c.key != key) {
+        std::vector<MaxSpan> spans;
+        max_spans(pk, pa.np, ranges, n_ranges, 0, spans);
+        if (upload_spans(c, key, spans, st)) return 1;
+    }
+    *spans_dev = (const MaxSpan *)c.dev.ptr; *n_spans = c.n;
+    return 0;
+}
+
 static int build_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkts, int64_t slab_lo, int64_t slab_hi,
                       void *out_dev, int mode, const int64_t *norm_ranges, int n_ranges, double *maxsq_dev,
                       void *stream) {
@@ -315,19 +347,23 @@ static int build_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *descs, int n_pkt
     a.out = (float2 *)out_dev; a.out_ld = 0;
     a.maxsq = reinterpret_cast<unsigned long long *>(maxsq_dev);
     a.mode = mode;
+    DeviceGuard g(ctx->device);
     if (mode == B200VEC_BUILD_MAXONLY) {
-        a.n_norm = 1; a.norm_lo[0] = slab_lo; a.norm_hi[0] = slab_hi;
         if (slab_hi == slab_lo) return 0;
+        const long long rg[2] = {slab_lo, slab_hi};
+        if (plan_max_spans(ctx, a.place, rg, 1, (cudaStream_t)stream, &a.spans, &a.n_spans)) return 1;
     } else if (mode == kSpNorm) {
         B2_REQUIRE(n_ranges >= 0 && n_ranges <= kWfMaxNormRanges && (n_ranges == 0 || norm_ranges), "bad norm ranges");
+        long long rg[2 * kWfMaxNormRanges];
+        int nr = 0;
         for (int r = 0; r < n_ranges; ++r) {
             const int64_t lo = norm_ranges[2 * r], hi = norm_ranges[2 * r + 1];
             B2_REQUIRE(lo >= 0 && hi >= lo, "bad norm range");
             if (hi == lo) continue;
-            a.norm_lo[a.n_norm] = lo; a.norm_hi[a.n_norm] = hi; ++a.n_norm;
+            rg[2 * nr] = lo; rg[2 * nr + 1] = hi; ++nr;
         }
+        if (plan_max_spans(ctx, a.place, rg, nr, (cudaStream_t)stream, &a.spans, &a.n_spans)) return 1;
     }
-    DeviceGuard g(ctx->device);
 #ifdef B2_AB
     if (mode != kSpNorm && ab_env("B200VEC_PLACE")) {      // round-1 kernel: needs both bank copies
         PlaceArgs pa;
@@ -449,11 +485,16 @@ int b200vec_batch_prepare(b200vec_ctx *ctx, const b200vec_batch_pkt *pkts, const
         h_pmax[j] = 0;
         if (job_len[j] > max_len) max_len = job_len[j];
     }
+    bs.h_pk.assign((size_t)n_vectors * stride, MaxSpanPacket{0, 1, 0, 0, 0});
+    bs.h_np.assign(n_vectors, 0);
+    bs.spans.n = -1;
     for (int v = 0; v < n_vectors; ++v) {
         int np = 0;
         for (int i = first[v]; i < first[v + 1]; ++i) {
             const b200vec_batch_pkt &q = pkts[i];
             if (q.count == 0) continue;
+            bs.h_pk[(size_t)v * stride + np] = MaxSpanPacket{q.start, q.period, q.count, job_len[pk_job[i]], q.flags & 1};
+            bs.h_np[v] = np + 1;
             PlaceDesc &p = h_desc[(size_t)v * stride + np++];
             p.start = q.start; p.period = q.period; p.count = q.count;
             p.len = (int)job_len[pk_job[i]];
@@ -480,7 +521,7 @@ int b200vec_batch_prepare(b200vec_ctx *ctx, const b200vec_batch_pkt *pkts, const
 int b200vec_batch_build(b200vec_ctx *ctx, int64_t total, void *out_dev, int64_t out_ld, int normalize,
                         double *maxsq_dev, void *stream) {
     B2_REQUIRE(ctx, "ctx is NULL");
-    const BatchState &bs = ctx->batch;
+    BatchState &bs = ctx->batch;
     B2_REQUIRE(bs.n_vec > 0 && bs.descs, "no prepared batch (call b200vec_batch_prepare first)");
     B2_REQUIRE(total >= 0 && (total == 0 || out_dev), "bad arguments");
     B2_REQUIRE(out_ld >= total && (out_ld & 1) == 0 && ((uintptr_t)out_dev & 15) == 0,
@@ -493,8 +534,22 @@ int b200vec_batch_build(b200vec_ctx *ctx, int64_t total, void *out_dev, int64_t 
     a.lo = 0; a.hi = total; a.out = (float2 *)out_dev; a.out_ld = out_ld;
     a.maxsq = reinterpret_cast<unsigned long long *>(maxsq_dev);
     a.mode = normalize ? kSpNorm : B200VEC_BUILD_STORE;
-    if (normalize) { a.n_norm = 1; a.norm_lo[0] = 0; a.norm_hi[0] = total; }
     DeviceGuard g(ctx->device);
+    if (normalize) {
+        // per vector: the ranges that hold its max (one common period of its trains + head and tail, or the whole
+        // vector), reduced to the spans under >= 2 instances (maxspans.cuh); planned once per (batch, total)
+        if (bs.spans.n < 0 || bs.spans.key != (unsigned long long)total) {
+            std::vector<MaxSpan> spans;
+            for (int v = 0; v < bs.n_vec; ++v) {
+                long long rg[4];
+                const MaxSpanPacket *pk = bs.h_pk.data() + (size_t)v * bs.pk_stride;
+                const int nr = max_eval_ranges(pk, bs.h_np[v], total, rg);
+                max_spans(pk, bs.h_np[v], rg, nr, v, spans);
+            }
+            if (upload_spans(bs.spans, (unsigned long long)total, spans, (cudaStream_t)stream)) return 1;
+        }
+        a.spans = (const MaxSpan *)bs.spans.dev.ptr; a.n_spans = bs.spans.n;
+    }
     if (normalize) B2_CUDA(cudaMemsetAsync(maxsq_dev, 0, sizeof(double) * bs.n_vec, (cudaStream_t)stream));
     return launch_span(ctx, a, (cudaStream_t)stream);
 }
@@ -619,7 +674,7 @@ static int build_stft1024_fm_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *desc
     B2_REQUIRE(n_frames * 512 <= slab_hi - slab_lo + 511, "frames must start inside the slab");
     WfArgs a;
     if (fill_place_args(ctx, descs, n_pkts, slab_lo, slab_hi, a.place)) return 1;
-    a.n_norm = 0; a.norm_units = 0; a.maxsq_out = nullptr; a.plain = 0;
+    a.spans = nullptr; a.n_spans = 0; a.maxsq_out = nullptr; a.plain = 0;
     a.world = 1; a.rank = 0; a.epoch = 0;
     for (int r = 0; r < kWfMaxPeers; ++r) a.peer[r] = nullptr;
     if (mode == kWfAutoNormPeer) {
@@ -631,18 +686,20 @@ static int build_stft1024_fm_impl(b200vec_ctx *ctx, const b200vec_pkt_desc *desc
         }
         a.world = world; a.rank = rank; a.epoch = epoch;
     }
+    DeviceGuard g(ctx->device);
     if (mode == kWfAutoNorm || mode == kWfAutoNormPeer) {
         B2_REQUIRE(n_ranges >= 0 && n_ranges <= kWfMaxNormRanges && (n_ranges == 0 || norm_ranges), "bad norm ranges");
+        long long rg[2 * kWfMaxNormRanges];
+        int nr = 0;
         for (int r = 0; r < n_ranges; ++r) {
             const int64_t lo = norm_ranges[2 * r], hi = norm_ranges[2 * r + 1];
             B2_REQUIRE(lo >= 0 && hi >= lo, "bad norm range");
             if (hi == lo) continue;
-            a.norm_lo[a.n_norm] = lo; a.norm_hi[a.n_norm] = hi; ++a.n_norm;
-            a.norm_units += (hi - lo + 1023) / 1024;
+            rg[2 * nr] = lo; rg[2 * nr + 1] = hi; ++nr;
         }
+        if (plan_max_spans(ctx, a.place, rg, nr, (cudaStream_t)stream, &a.spans, &a.n_spans)) return 1;
         a.maxsq_out = maxsq_dev;
     }
-    DeviceGuard g(ctx->device);
     a.vec = (float2 *)vec_out_dev;
     a.maxsq = reinterpret_cast<const unsigned long long *>(maxsq_dev);
     a.mode = mode;

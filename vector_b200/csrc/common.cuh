@@ -10,6 +10,7 @@
 #include <map>
 
 #include "../../include/b200vec.h"
+#include "maxspans.cuh"
 
 namespace b200vec {
 
@@ -67,6 +68,13 @@ struct Scratch {
     size_t bytes = 0;
 };
 
+// Uploaded must-evaluate span list of the max pass (maxspans.cuh), reused while the planner's inputs do not change
+struct SpanCache {
+    Scratch dev;
+    unsigned long long key = 0;
+    long long n = -1;           // -1: nothing uploaded
+};
+
 // State of a prepared scenario batch (b200vec_batch_prepare -> b200vec_batch_build, span.cuh)
 struct BatchState {
     Scratch bank;               // shifted packets, one copy each, 16-byte aligned starts
@@ -76,6 +84,9 @@ struct BatchState {
     const void *descs = nullptr;
     const int *np = nullptr;
     int n_vec = 0, pk_stride = 0, n_jobs = 0;
+    std::vector<MaxSpanPacket> h_pk;    // host copy of the placement descriptors, [n_vec][pk_stride] (max-span planner)
+    std::vector<int> h_np;
+    SpanCache spans;                    // per-vector must-evaluate spans for the `total` of the last normalised build
 };
 
 // Top-histogram state kept between b200vec_select_begin and b200vec_select_finish
@@ -100,6 +111,7 @@ struct b200vec_ctx {
     unsigned int *wf_ctr = nullptr;       // work-item counter of the warp-per-frame kernel (wf1024.cuh)
     unsigned int *sp_ctr = nullptr;       // work-item counter / grid barrier of the span kernel (span.cuh)
     b200vec::BatchState batch;            // prepared scenario batch
+    b200vec::SpanCache max_spans;         // must-evaluate spans of the last normalised single-vector build
     unsigned int *top_hist = nullptr;     // [kTopBins] u32 + one u64 (+0 count) + one u64 (candidate count)
     b200vec::Scratch cand;                // candidate array of the fast select
     b200vec::TopState top;

@@ -40,9 +40,8 @@ struct SpanArgs {
     long long out_ld;
     unsigned long long *maxsq;   // [n_vec] bits of max |v|^2 (double): MAXONLY / NORM raise it, SCALE / NORM read it
     int mode;                    // B200VEC_BUILD_STORE | _MAXONLY | _SCALE | kSpNorm
-    long long norm_lo[kWfMaxNormRanges], norm_hi[kWfMaxNormRanges];   // MAXONLY / NORM: ranges evaluated (every vector)
-    int n_norm;
-    long long norm_units;        // 1024-sample units per vector over all ranges
+    const MaxSpan *spans;        // MAXONLY / NORM: the spans evaluated (maxspans.cuh), sorted by vector
+    long long n_spans;
     unsigned int *ctr;           // [0] next work item, [2] grid barrier; zeroed on the stream before every launch
 };
 
@@ -71,32 +70,6 @@ __device__ __forceinline__ void sp_overlap(const SpanArgs &a, const PlaceDesc *d
     }
 }
 
-// Pass A only: the 512 samples at `off` lie inside exactly ONE instance of a packet whose whole-packet
-// max is attained elsewhere in the vector (PlaceDesc::free_inst) -> nothing to read (wf_norm_can_skip).
-template <bool BATCH>
-__device__ __forceinline__ bool sp_can_skip(const SpanArgs &a, const PlaceDesc *dv, unsigned active, int cnt_l,
-                                            int rel0_l, int off) {
-    int n_ov = 0;
-    bool ok = false;
-    for (unsigned m = active; m; m &= m - 1) {
-        const int p = __ffs(m) - 1;
-        const int cnt = __shfl_sync(0xffffffffu, cnt_l, p);
-        const int rel0 = __shfl_sync(0xffffffffu, rel0_l, p);
-        const PlaceDesc &d = sp_desc<BATCH>(a, dv, p);
-        const int len = d.len;
-        const long long period = d.period;
-        const bool fr = d.free_inst != 0;
-        long long r64 = (long long)rel0 + off;
-        for (int i = 0; i < cnt; ++i, r64 -= period) {
-            if (r64 + 512 <= 0) break;
-            if (r64 >= len) continue;
-            ++n_ov;
-            ok = fr && r64 >= 0 && r64 + 512 <= len;
-        }
-    }
-    return n_ov == 1 && ok;
-}
-
 // B: the 512 samples starting `off` samples into the item; false when nothing overlaps them (x == 0).
 template <bool BATCH>
 __device__ __forceinline__ bool sp_build_half(const SpanArgs &a, const PlaceDesc *dv, unsigned active, int cnt_l,
@@ -123,7 +96,7 @@ __device__ __forceinline__ bool sp_build_half(const SpanArgs &a, const PlaceDesc
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                     const float2 v = wf_ldg_keep(base + 32 * j, keep);
-                    x[j].x += v.x; x[j].y += v.y;
+                    x[j] = __fadd2_rn(x[j], v);
                 }
             } else {
 #pragma unroll
@@ -131,7 +104,7 @@ __device__ __forceinline__ bool sp_build_half(const SpanArgs &a, const PlaceDesc
                     const int n = r + lane + 32 * j;
                     if (n >= 0 && n < len) {
                         const float2 v = wf_ldg_keep(base + 32 * j, keep);
-                        x[j].x += v.x; x[j].y += v.y;
+                        x[j] = __fadd2_rn(x[j], v);
                     }
                 }
             }
@@ -157,13 +130,15 @@ span_kernel(const __grid_constant__ SpanArgs a) {
 
     if (a.mode == B200VEC_BUILD_MAXONLY || a.mode == kSpNorm) {
         // ---------------------------------------------------------------- pass A: max |v|^2 per vector, no stores
-        const long long total_units = a.norm_units * a.n_vec;
+        // every warp takes one contiguous run of the list: consecutive spans mostly belong to one vector
+        const long long per = (a.n_spans + nw - 1) / nw;
+        const long long u1 = (gw + 1) * per < a.n_spans ? (gw + 1) * per : a.n_spans;
         double tmax = 0.0;                                   // running max of |v|^2 for vector cur_v (exact products in fp64)
         float fthr = 0.0f;                                   // fp32 pre-filter threshold
         int cur_v = -1;
-        for (long long u = gw; u < total_units; u += nw) {
-            const int v = BATCH ? (int)(u / a.norm_units) : 0;
-            long long w = BATCH ? u - (long long)v * a.norm_units : u;
+        for (long long u = gw * per; u < u1; ++u) {
+            const MaxSpan sp = a.spans[u];
+            const int v = BATCH ? sp.vec : 0;
             if (v != cur_v) {
                 if (cur_v >= 0) {
                     tmax = warp_max(tmax);
@@ -171,32 +146,20 @@ span_kernel(const __grid_constant__ SpanArgs a) {
                 }
                 cur_v = v; tmax = 0.0; fthr = 0.0f;
             }
-            long long s0 = 0, s1 = 0;
-            for (int r = 0; r < a.n_norm; ++r) {
-                const long long nu = (a.norm_hi[r] - a.norm_lo[r] + 1023) / 1024;
-                if (w < nu) { s0 = a.norm_lo[r] + w * 1024; s1 = a.norm_hi[r]; break; }
-                w -= nu;
-            }
-            if (s1 > s0 + 1024) s1 = s0 + 1024;
             const PlaceDesc *dv = BATCH ? a.gdesc + (long long)v * a.pk_stride : nullptr;
             const int np = BATCH ? a.gnp[v] : a.place.np;
             int cnt_l, rel0_l;
-            sp_overlap<BATCH>(a, dv, np, lane, s0, 1024, cnt_l, rel0_l);
+            sp_overlap<BATCH>(a, dv, np, lane, sp.s0, 512, cnt_l, rel0_l);
             const unsigned active = __ballot_sync(0xffffffffu, cnt_l > 0);
             if (!active) continue;
-            for (int half = 0; half < 2; ++half) {
-                const int valid = (int)(s1 - s0) - 512 * half;
-                if (valid <= 0) break;
-                float2 x[16];
-                if (sp_can_skip<BATCH>(a, dv, active, cnt_l, rel0_l, 512 * half)) continue;
-                if (!sp_build_half<BATCH>(a, dv, active, cnt_l, rel0_l, 512 * half, lane, x, keep)) continue;
+            float2 x[16];
+            if (!sp_build_half<BATCH>(a, dv, active, cnt_l, rel0_l, 0, lane, x, keep)) continue;
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const float q = x[j].x * x[j].x + x[j].y * x[j].y;
-                    if (lane + 32 * j < valid && q >= fthr) {          // samples past the range end never enter the max
-                        const double e = (double)x[j].x * (double)x[j].x + (double)x[j].y * (double)x[j].y;
-                        if (e > tmax) { tmax = e; fthr = q * 0.99999f; }
-                    }
+            for (int j = 0; j < 16; ++j) {
+                const float q = x[j].x * x[j].x + x[j].y * x[j].y;
+                if (lane + 32 * j < sp.n && q >= fthr) {             // samples past the span's end never enter the max
+                    const double e = (double)x[j].x * (double)x[j].x + (double)x[j].y * (double)x[j].y;
+                    if (e > tmax) { tmax = e; fthr = q * 0.99999f; }
                 }
             }
         }
@@ -274,17 +237,15 @@ inline int span_setup() {
     return 0;
 }
 
-// a.place (or gdesc/gnp), n_vec, lo/hi, out, maxsq, mode and the norm ranges are filled by the caller.
+// a.place (or gdesc/gnp), n_vec, lo/hi, out, maxsq, mode and the max-pass span list are filled by the caller.
 inline int launch_span(b200vec_ctx *ctx, SpanArgs &a, cudaStream_t st) {
     const long long n = a.hi - a.lo;
     if (a.n_vec <= 0) return 0;
     const bool batch = a.gdesc != nullptr;
     const bool pass_a = a.mode == B200VEC_BUILD_MAXONLY || a.mode == kSpNorm;
     const bool pass_b = a.mode != B200VEC_BUILD_MAXONLY;
-    a.norm_units = 0;
-    if (pass_a)
-        for (int r = 0; r < a.n_norm; ++r) a.norm_units += (a.norm_hi[r] - a.norm_lo[r] + 1023) / 1024;
-    if ((!pass_b || n <= 0) && a.norm_units == 0) return 0;
+    if (!pass_a) { a.spans = nullptr; a.n_spans = 0; }
+    if ((!pass_b || n <= 0) && a.n_spans == 0 && !pass_a) return 0;
     B2_REQUIRE(!pass_b || n <= 0 || (((uintptr_t)a.out & 15) == 0 && (a.n_vec == 1 || (a.out_ld & 1) == 0)),
                "output must be 16-byte aligned (and the vector pitch even)");
     if (!ctx->sp_ctr) B2_CUDA(cudaMalloc(&ctx->sp_ctr, 4 * sizeof(unsigned int)));
@@ -298,7 +259,7 @@ inline int launch_span(b200vec_ctx *ctx, SpanArgs &a, cudaStream_t st) {
     }
     const long long halves = n > 0 ? (n + 511) / 512 : 0;
     const long long items = pass_b ? (halves + kSpChunk - 1) / kSpChunk * a.n_vec : 0;
-    const long long units = a.norm_units * a.n_vec;
+    const long long units = a.n_spans;
     const long long work = items > units ? items : units;
     const long long cap = (long long)ctx->sm_count * occ[batch];       // one full wave: persistent warps, dynamic items
     long long grid = (work + kSpWarps - 1) / kSpWarps;

@@ -47,6 +47,7 @@
 #include "fft32.cuh"
 #include "stft1024.cuh"      // get_tw1024
 #include "fused1024.cuh"     // tma_bulk_s2g, tma_store_commit
+#include "maxspans.cuh"
 
 namespace b200vec {
 
@@ -82,10 +83,10 @@ struct WfArgs {
     int *flag;
     long long n_big;             // work items [0, n_big) are CHUNK frames long, the rest one frame
     long long n_chunks;
-    // in-kernel normalisation (mode == kWfAutoNorm): max |v|^2 over these sample ranges first
-    long long norm_lo[kWfMaxNormRanges], norm_hi[kWfMaxNormRanges];
-    long long norm_units;        // 1024-sample units over all ranges (a range's last unit may be partial)
-    int n_norm;
+    // in-kernel normalisation (mode == kWfAutoNorm[Peer]): max |v|^2 over these spans first — the pieces of the
+    // caller's norm ranges that can hold the max (maxspans.cuh; device memory owned by the context)
+    const MaxSpan *spans;
+    long long n_spans;
     double *maxsq_out;           // receives max |v|^2 (may be NULL)
     int plain;                   // host side: launch the PLAIN instantiation
     // kWfAutoNormPeer: one symmetric 64-byte block per GPU, peer[r] = rank r's block mapped here:
@@ -121,30 +122,6 @@ __device__ __forceinline__ unsigned long long wf_policy_evict_first() {
 __device__ __forceinline__ void wf_bulk_s2g(void *dst, unsigned src, unsigned bytes, unsigned long long pol) {
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
                  ::"l"(dst), "r"(src), "r"(bytes), "l"(pol) : "memory");
-}
-
-// Pass A only: true when the 512 samples at `off` lie inside exactly ONE instance, of a packet whose
-// whole-packet max is known to be attained elsewhere in the vector (PlaceDesc::free_inst) — their
-// |v|^2 cannot exceed that max (it enters the reduction through PlaceDesc::pmax), so nothing is read.
-__device__ __forceinline__ bool wf_norm_can_skip(const WfArgs &a, unsigned active, int cnt_l, int rel0_l, int off) {
-    int n_ov = 0;
-    bool ok = false;
-    for (unsigned m = active; m; m &= m - 1) {
-        const int p = __ffs(m) - 1;
-        const int cnt = __shfl_sync(0xffffffffu, cnt_l, p);
-        const int rel0 = __shfl_sync(0xffffffffu, rel0_l, p);
-        const PlaceDesc &d = a.place.d[p];
-        const int len = d.len;
-        const long long period = d.period;
-        long long r64 = (long long)rel0 + off;
-        for (int i = 0; i < cnt; ++i, r64 -= period) {
-            if (r64 + 512 <= 0) break;
-            if (r64 >= len) continue;
-            ++n_ov;
-            ok = d.free_inst && r64 >= 0 && r64 + 512 <= len;
-        }
-    }
-    return n_ov == 1 && ok;
 }
 
 // B: the 512 samples starting `off` samples into the item's span.  Returns false when no packet
@@ -295,26 +272,22 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
     }
     __syncthreads();
     if (!PLAIN && (a.mode == kWfAutoNorm || a.mode == kWfAutoNormPeer)) {
-        // Pass A inside the kernel (single-GPU builds): every warp evaluates its share of the ranges whose
-        // max is the max of the whole vector (hostmath.max_eval_ranges), the grid meets at a barrier
-        // (cooperative launch: all CTAs are resident), and everybody reads the same exact max.
+        // Pass A inside the kernel: every warp evaluates its share of the spans that can hold the max of the
+        // whole vector (maxspans.cuh: the pieces of hostmath.max_eval_ranges under >= 2 instances; what lies
+        // under one instance is covered by the packet maxima below), the grid meets at a barrier (cooperative
+        // launch: all CTAs are resident), and everybody reads the same exact max.
         unsigned long long *slot = reinterpret_cast<unsigned long long *>(a.ctr + 4);
         double tmax = 0.0;                                   // running max of |v|^2 (exact products in fp64)
         float fthr = 0.0f;                                   // fp32 pre-filter threshold
         const long long gw = (long long)blockIdx.x * kWfWarps + warp, nw = (long long)gridDim.x * kWfWarps;
-        for (long long u = gw; u < a.norm_units; u += nw) {
-            long long v = u, s0 = 0, s1 = 0;
-            for (int r = 0; r < a.n_norm; ++r) {
-                const long long nu = (a.norm_hi[r] - a.norm_lo[r] + 1023) / 1024;
-                if (v < nu) { s0 = a.norm_lo[r] + v * 1024; s1 = a.norm_hi[r]; break; }
-                v -= nu;
-            }
-            if (s1 > s0 + 1024) s1 = s0 + 1024;
+        for (long long u = gw; u < a.n_spans; u += nw) {
+            const MaxSpan sp = a.spans[u];
+            const long long s0 = sp.s0;
             int cnt_l = 0, rel0_l = 0;
             if (lane < a.place.np) {
                 const PlaceDesc &d = a.place.d[lane];
                 long long klo = floor_div(s0 - d.len - d.start, d.period) + 1;
-                long long khi = floor_div(s0 + 1024 - 1 - d.start, d.period);
+                long long khi = floor_div(s0 + 512 - 1 - d.start, d.period);
                 if (klo < 0) klo = 0;
                 if (khi > d.count - 1) khi = d.count - 1;
                 const long long cn = khi - klo + 1;
@@ -322,19 +295,14 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                 rel0_l = cnt_l ? (int)(s0 - (d.start + klo * d.period)) : 0;
             }
             const unsigned active = __ballot_sync(0xffffffffu, cnt_l > 0);
-            for (int half = 0; half < 2; ++half) {
-                const int valid = (int)(s1 - s0) - 512 * half;
-                if (valid <= 0) break;
-                float2 x[16];
-                if (wf_norm_can_skip(a, active, cnt_l, rel0_l, 512 * half)) continue;
-                if (!wf_build_half(a, active, cnt_l, rel0_l, 512 * half, lane, x, keep)) continue;
+            float2 x[16];
+            if (!wf_build_half(a, active, cnt_l, rel0_l, 0, lane, x, keep)) continue;
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const float q = x[j].x * x[j].x + x[j].y * x[j].y;
-                    if (lane + 32 * j < valid && q >= fthr) {      // samples past the range end never enter the max
-                        const double e = (double)x[j].x * (double)x[j].x + (double)x[j].y * (double)x[j].y;
-                        if (e > tmax) { tmax = e; fthr = q * 0.99999f; }
-                    }
+            for (int j = 0; j < 16; ++j) {
+                const float q = x[j].x * x[j].x + x[j].y * x[j].y;
+                if (lane + 32 * j < sp.n && q >= fthr) {           // samples past the span's end never enter the max
+                    const double e = (double)x[j].x * (double)x[j].x + (double)x[j].y * (double)x[j].y;
+                    if (e > tmax) { tmax = e; fthr = q * 0.99999f; }
                 }
             }
         }
