@@ -105,6 +105,67 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+class NvmlSampler:
+    """Clocks / throttle reasons through NVML, polled every few milliseconds from a thread: the timed region is a
+    few milliseconds long, far below nvidia-smi's practical sampling period.  Falls back to ClockSampler."""
+    REASONS = (("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40), ("sw_power_cap", 0x4))
+
+    def __init__(self, index, period_s=0.003):
+        self.index, self.period, self.rows, self.thread, self.stop_flag, self.fallback = index, period_s, [], None, False, None
+        self.h = None
+
+    def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else self.index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.nv = pynvml
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.h = None
+            self.fallback = ClockSampler(self.index)
+            self.fallback.start()
+
+    def _poll(self):
+        nv = self.nv
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            try:
+                t = time.perf_counter()
+                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                rs = get_reasons(self.h)
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                except Exception:
+                    pw = None
+                self.rows.append((t, float(sm), int(rs), pw))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def window(self, t0, t1):
+        """Summary of the samples taken in [t0, t1] (perf_counter seconds)."""
+        if self.h is None:
+            return None
+        rows = [r for r in self.rows if t0 <= r[0] <= t1]
+        reasons = sorted({name for r in rows for name, bit in self.REASONS if r[2] & bit})
+        pw = [r[3] for r in rows if r[3] is not None]
+        return {"sm_mhz": float(np.median([r[1] for r in rows])) if rows else None,
+                "sm_min_mhz": min(r[1] for r in rows) if rows else None, "sm_max_mhz": self.mx,
+                "reasons": reasons, "samples": len(rows), "power_w_max": max(pw) if pw else None,
+                "source": "NVML (clock, clocks-event reasons, power), polled every %d ms" % round(self.period * 1e3)}
+
+    def stop(self):
+        self.stop_flag = True
+        if self.fallback is not None:
+            return self.fallback.stop()
+        return None
+
+
 def workload(n_gpus):
     from vector_b200 import synth
     cfgs, packets = synth.scenario(synth.CFG2_ROWS, FS)
@@ -478,36 +539,57 @@ def run_ours(args):
             graph.replay()
         else:
             step()
-    # Clocks: the timed region is a few milliseconds, far below nvidia-smi's sampling period, so the SAME step
-    # keeps the GPU busy for ~0.5 s before it and ~0.3 s after it (fixed iteration counts: identical on every
-    # rank) while rank 0 samples clocks and throttle reasons every 100 ms.
-    sampler = ClockSampler(local)
+    # Timed region (the contract): W warm-up steps (above), then EXACTLY K steps between barrier + synchronize pairs.
+    # The step is one kernel launch timed on its own, so the roofline denominator is the BURST copy bandwidth of
+    # MEASURED_PEAKS.json and the timed region is taken the same way: the GPU is busy with the same step for
+    # ~50 ms before and after it (steady clocks, warm L2 bank; identical iteration counts on every rank), far
+    # below the ~0.3 s of continuous load after which this kernel reaches the 1000 W power cap.  NVML is polled
+    # every 3 ms by a thread on rank 0: `clocks` is what was seen from the start of the pre-load to the end of the
+    # post-load.  The SUSTAINED behaviour (same K steps after `--load-steps` steps of continuous load, SM clocks
+    # settled under sw_power_cap) is measured right after and reported beside it as `sustained`.
+    sampler = NvmlSampler(local)
     if rank == 0:
         sampler.start()
-    barrier()
-    for _ in range(args.load_steps):
-        run_one()
-    barrier()
+    short = max(args.burst_steps, 0)
+
+    def timed(pre, post):
+        barrier()
+        w0 = time.perf_counter()
+        for _ in range(pre):
+            run_one()
+        barrier()
+        t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_start.record()
+        for _ in range(args.steps):
+            run_one()
+        t_end.record()
+        barrier()
+        ms = t_start.elapsed_time(t_end)
+        for _ in range(post):
+            run_one()
+        barrier()
+        return ms, (w0, time.perf_counter())
+
     launches0 = eng.launches
-    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_start.record()
-    for _ in range(args.steps):
-        run_one()
-    t_end.record()
-    barrier()
-    ms_total = t_start.elapsed_time(t_end)
-    for _ in range(args.load_steps * 3 // 5):
-        run_one()
-    barrier()
-    launches = launches_per_step * args.steps if graph is not None else eng.launches - launches0
-    clocks = sampler.stop() if rank == 0 else None
-    if clocks is not None:
-        clocks["window"] = (f"{args.load_steps} untimed steps before + the timed region + {args.load_steps * 3 // 5} after, "
-                            "GPU continuously busy with the same step; nvidia-smi every 100 ms")
-    ms_t = torch.tensor([ms_total], dtype=torch.float64, device=eng.device)
+    ms_total, win_burst = timed(short, short)
+    launches = launches_per_step * args.steps if graph is not None else (eng.launches - launches0) * args.steps // (2 * short + args.steps)
+    ms_sust, win_sust = timed(args.load_steps, args.load_steps * 3 // 5)
+    clocks = sustained_clocks = None
+    if rank == 0:
+        clocks, sustained_clocks = sampler.window(*win_burst), sampler.window(*win_sust)
+        fb = sampler.stop()
+        if clocks is None:                               # no NVML: nvidia-smi over both windows
+            clocks = sustained_clocks = fb
+        if clocks is not None:
+            clocks["window"] = (f"{short} untimed steps + the {args.steps} timed steps + {short} untimed steps, GPU continuously "
+                                "busy with the same step")
+        if sustained_clocks is not None and sustained_clocks is not clocks:
+            sustained_clocks["window"] = (f"{args.load_steps} untimed steps + {args.steps} timed steps + "
+                                          f"{args.load_steps * 3 // 5} untimed steps of continuous load")
+    ms_t = torch.tensor([ms_total, ms_sust], dtype=torch.float64, device=eng.device)
     if world > 1:
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
-    ms_step = ms_t.item() / args.steps
+    ms_step, ms_step_sust = (ms_t / args.steps).tolist()
     peer_status = eng.peer_status() if peer is not None else 0
 
     # ---- e2e through the host-buffer API: H2D packets, D2H vector + spectrogram, every step
@@ -618,6 +700,11 @@ def run_ours(args):
                     "raw_d2h_ms": d2h_ms.item(), "raw_d2h_GBps_per_gpu": d2h / d2h_ms.item() / 1e6,
                     "raw_d2h_note": "the same two pinned copies alone, all ranks at once: the platform's PCIe / host-memory ceiling for this step"},
             "gpu_launches": launches, "clocks": clocks,
+            "sustained": {"ms_per_step": ms_step_sust, "value": total / (ms_step_sust * 1e-3) / 1e9, "unit": "GSa/s",
+                          "roofline_frac": fused_bytes / (ms_step_sust * 1e-3) / 1e9 / peak, "clocks": sustained_clocks,
+                          "note": "the same K steps after --load-steps steps of continuous load: the kernel then runs at the "
+                                  "1000 W power cap with lower SM clocks (sw_power_cap); `value` above is the burst figure, "
+                                  "like the copy bandwidth it is compared with"},
             "cfg4": cfg4, "cfg5": cfg5, "save": save,
         }
         if world == 1 and not args.no_cpu:
@@ -660,6 +747,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--load-steps", type=int, default=2500,
                     help="untimed steps run around the timed region so that nvidia-smi can sample clocks under load")
+    ap.add_argument("--burst-steps", type=int, default=300,
+                    help="untimed steps right before and after the timed region (steady clocks, ~50 ms each side)")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replays")
     ap.add_argument("--peer-max", action="store_true",
                     help="A/B at N>1: each rank evaluates its SHARE of the max ranges and the maxima are MAX-combined inside the "

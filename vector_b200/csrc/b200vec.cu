@@ -175,6 +175,11 @@ int b200vec_destroy(b200vec_ctx *ctx) {
     if (ctx->batch.bank.ptr) cudaFree(ctx->batch.bank.ptr);
     if (ctx->batch.tables.ptr) cudaFree(ctx->batch.tables.ptr);
     if (ctx->batch.pin) cudaFreeHost(ctx->batch.pin);
+    for (SpanCache *c : {&ctx->batch.spans, &ctx->max_spans}) {
+        if (c->dev.ptr) cudaFree(c->dev.ptr);
+        if (c->pin) cudaFreeHost(c->pin);
+        if (c->pin_free) cudaEventDestroy(c->pin_free);
+    }
     if (ctx->slot_max) cudaFree(ctx->slot_max);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     delete ctx;
@@ -308,8 +313,20 @@ static int upload_spans(SpanCache &c, unsigned long long key, const std::vector<
                "the max-span list of this (descriptors, ranges) pair is not uploaded yet: run the step once before capturing it in a CUDA graph");
     if (ensure_scratch(c.dev, (spans.size() + 1) * sizeof(MaxSpan))) return 1;
     c.n = -1;
-    if (!spans.empty())          // pageable source: the call returns once the data is staged
-        B2_CUDA(cudaMemcpyAsync(c.dev.ptr, spans.data(), spans.size() * sizeof(MaxSpan), cudaMemcpyHostToDevice, st));
+    if (!spans.empty()) {
+        const size_t bytes = spans.size() * sizeof(MaxSpan);
+        if (!c.pin_free) B2_CUDA(cudaEventCreateWithFlags(&c.pin_free, cudaEventDisableTiming));
+        else B2_CUDA(cudaEventSynchronize(c.pin_free));               // the previous upload has left the staging block
+        if (c.pin_bytes < bytes) {
+            if (c.pin) cudaFreeHost(c.pin);
+            c.pin = nullptr; c.pin_bytes = 0;
+            B2_CUDA(cudaMallocHost(&c.pin, bytes + bytes / 4));
+            c.pin_bytes = bytes + bytes / 4;
+        }
+        memcpy(c.pin, spans.data(), bytes);
+        B2_CUDA(cudaMemcpyAsync(c.dev.ptr, c.pin, bytes, cudaMemcpyHostToDevice, st));
+        B2_CUDA(cudaEventRecord(c.pin_free, st));
+    }
     c.key = key; c.n = (long long)spans.size();
     return 0;
 }
@@ -487,7 +504,6 @@ int b200vec_batch_prepare(b200vec_ctx *ctx, const b200vec_batch_pkt *pkts, const
     }
     bs.h_pk.assign((size_t)n_vectors * stride, MaxSpanPacket{0, 1, 0, 0, 0});
     bs.h_np.assign(n_vectors, 0);
-    bs.spans.n = -1;
     for (int v = 0; v < n_vectors; ++v) {
         int np = 0;
         for (int i = first[v]; i < first[v + 1]; ++i) {
@@ -538,7 +554,9 @@ int b200vec_batch_build(b200vec_ctx *ctx, int64_t total, void *out_dev, int64_t 
     if (normalize) {
         // per vector: the ranges that hold its max (one common period of its trains + head and tail, or the whole
         // vector), reduced to the spans under >= 2 instances (maxspans.cuh); planned once per (batch, total)
-        if (bs.spans.n < 0 || bs.spans.key != (unsigned long long)total) {
+        long long tt[2] = {0, total};
+        const unsigned long long key = max_spans_key(bs.h_pk.data(), (int)bs.h_pk.size(), tt, 1);
+        if (bs.spans.n < 0 || bs.spans.key != key) {
             std::vector<MaxSpan> spans;
             for (int v = 0; v < bs.n_vec; ++v) {
                 long long rg[4];
@@ -546,7 +564,7 @@ int b200vec_batch_build(b200vec_ctx *ctx, int64_t total, void *out_dev, int64_t 
                 const int nr = max_eval_ranges(pk, bs.h_np[v], total, rg);
                 max_spans(pk, bs.h_np[v], rg, nr, v, spans);
             }
-            if (upload_spans(bs.spans, (unsigned long long)total, spans, (cudaStream_t)stream)) return 1;
+            if (upload_spans(bs.spans, key, spans, (cudaStream_t)stream)) return 1;
         }
         a.spans = (const MaxSpan *)bs.spans.dev.ptr; a.n_spans = bs.spans.n;
     }

@@ -71,6 +71,9 @@ struct Scratch {
 // Uploaded must-evaluate span list of the max pass (maxspans.cuh), reused while the planner's inputs do not change
 struct SpanCache {
     Scratch dev;
+    void *pin = nullptr;        // pinned staging block of the upload
+    size_t pin_bytes = 0;
+    cudaEvent_t pin_free = nullptr;     // recorded after the upload that reads `pin`
     unsigned long long key = 0;
     long long n = -1;           // -1: nothing uploaded
 };
