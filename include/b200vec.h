@@ -242,6 +242,12 @@ int b200vec_peer_status(b200vec_ctx *ctx, int *status_host, void *stream);
  *           select_count() then select_ranks().  Both synchronise the stream. */
 int b200vec_db(b200vec_ctx *ctx, const float *s_dev, int64_t n, float floor_val,
                float *out_dev, void *stream);
+/* b200vec_db plus the same map applied to n_values (<= 8) host values in the same launch:
+ * values_out_host[i] = 10*log10(|values_host[i]| + floor) computed by the kernel's own instruction sequence —
+ * normalize_spectrogram's vmin / vmax (utils.py:372-373) are then dB-image values bit for bit, found as order
+ * statistics of |S| (dB is monotone in |S|).  Synchronises the stream when n_values > 0. */
+int b200vec_db_values(b200vec_ctx *ctx, const float *s_dev, int64_t n, float floor_val, float *out_dev,
+                      const float *values_host, int n_values, float *values_out_host, void *stream);
 int b200vec_select_count(b200vec_ctx *ctx, const float *data_dev, int64_t n, int positive_only,
                          int64_t *count_host, void *stream);
 int b200vec_select_ranks(b200vec_ctx *ctx, const float *data_dev, int64_t n, int positive_only,

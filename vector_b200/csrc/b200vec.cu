@@ -86,6 +86,7 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
+constexpr long long kSelSmallMax = 16LL << 20;   // elements: at or below, the select runs as one cooperative launch
 constexpr size_t kPinnedBytes = 64 * 1024;       // select state, the 13-bit histogram (32 KB + 16 B), small results
 
 static int run_select(b200vec_ctx *ctx, const float *data, long long n, int flags,
@@ -96,6 +97,21 @@ static int run_select(b200vec_ctx *ctx, const float *data, long long n, int flag
     init.n_ranks = nr;
     for (int r = 0; r < nr; ++r) init.resid[r] = (unsigned long long)ranks[r];
     sel_init<<<1, 1, 0, st>>>(ctx->hist, init);
+    if (n > 0 && n <= kSelSmallMax) {
+        // candidate arrays, previews: the three histogram reads cost less than six dependent launches — one
+        // cooperative launch with grid barriers between the levels
+        long long blocks = (n / 4 + kPickThreads * kSelUnroll - 1) / (kPickThreads * kSelUnroll);
+        if (blocks > ctx->sm_count) blocks = ctx->sm_count;
+        if (blocks < 1) blocks = 1;
+        const size_t smem = (size_t)(nr * kBins2 > kBins1 ? nr * kBins2 : kBins1) * sizeof(unsigned int);
+        void *kargs[] = {(void *)&data, (void *)&n, (void *)&flags, (void *)&ctx->hist};
+        B2_CUDA(cudaLaunchCooperativeKernel((const void *)sel_small_kernel, dim3((unsigned)blocks), dim3(kPickThreads),
+                                            kargs, smem, st));
+        B2_CUDA(cudaMemcpyAsync(ctx->pinned, ctx->hist + kStateOff, sizeof(SelState), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaStreamSynchronize(st));
+        memcpy(host_state, ctx->pinned, sizeof(SelState));
+        return 0;
+    }
     const unsigned grid = (unsigned)(ctx->sm_count * 8);
     if (n > 0) sel_hist1<<<grid, kSelThreads, 0, st>>>(data, n, flags, ctx->hist);
     sel_pick<1><<<1, kPickThreads, 0, st>>>(ctx->hist);
@@ -146,6 +162,8 @@ int b200vec_create(int device, b200vec_ctx **out) {
                                  B200VEC_MAX_RANKS * kBins2 * 4));
     B2_CUDA(cudaFuncSetAttribute(sel_histN<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  B200VEC_MAX_RANKS * kBins3 * 4));
+    B2_CUDA(cudaFuncSetAttribute(sel_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 B200VEC_MAX_RANKS * kBins2 * 4));
     B2_CUDA(cudaFuncSetAttribute(stft_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  200 * 1024));
     if (stft1024_setup() || fused1024_setup() || wf1024_setup() || span_setup()) { delete ctx; return 1; }
@@ -786,17 +804,40 @@ int b200vec_stft1024_fm(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin,
 }
 
 // ---------------------------------------------------------------------------------------
-int b200vec_db(b200vec_ctx *ctx, const float *s_dev, int64_t n, float floor_val,
-               float *out_dev, void *stream) {
+static int db_impl(b200vec_ctx *ctx, const float *s_dev, int64_t n, float floor_val, float *out_dev,
+                   const float *values_host, int n_values, float *values_out_host, cudaStream_t st) {
     B2_REQUIRE(ctx && (n == 0 || (s_dev && out_dev)), "NULL argument");
-    if (n == 0) return 0;
+    B2_REQUIRE(n_values >= 0 && n_values <= B200VEC_MAX_RANKS && (n_values == 0 || (values_host && values_out_host)),
+               "bad value list");
+    if (n == 0 && n_values == 0) return 0;
     DeviceGuard g(ctx->device);
-    long long grid = (n + kSelThreads - 1) / kSelThreads;
+    DbExtra ex;
+    memset(&ex, 0, sizeof(ex));
+    ex.n = n_values;
+    for (int i = 0; i < n_values; ++i) ex.v[i] = values_host[i];
+    long long grid = (n / 4 + kSelThreads - 1) / kSelThreads;
     const long long cap = (long long)ctx->sm_count * 16;
     if (grid > cap) grid = cap;
-    db_kernel<<<(unsigned)grid, kSelThreads, 0, (cudaStream_t)stream>>>(s_dev, n, floor_val, out_dev);
+    if (grid < 1) grid = 1;
+    float *ex_dev = reinterpret_cast<float *>(ctx->hist + kBarrierOff + 4);        // B200VEC_MAX_RANKS floats of scratch
+    db_kernel<<<(unsigned)grid, kSelThreads, 0, st>>>(s_dev, n, floor_val, out_dev, ex, ex_dev);
     B2_CUDA(cudaGetLastError());
+    if (n_values > 0) {
+        B2_CUDA(cudaMemcpyAsync(ctx->pinned, ex_dev, sizeof(float) * n_values, cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaStreamSynchronize(st));
+        memcpy(values_out_host, ctx->pinned, sizeof(float) * n_values);
+    }
     return 0;
+}
+
+int b200vec_db(b200vec_ctx *ctx, const float *s_dev, int64_t n, float floor_val,
+               float *out_dev, void *stream) {
+    return db_impl(ctx, s_dev, n, floor_val, out_dev, nullptr, 0, nullptr, (cudaStream_t)stream);
+}
+
+int b200vec_db_values(b200vec_ctx *ctx, const float *s_dev, int64_t n, float floor_val, float *out_dev,
+                      const float *values_host, int n_values, float *values_out_host, void *stream) {
+    return db_impl(ctx, s_dev, n, floor_val, out_dev, values_host, n_values, values_out_host, (cudaStream_t)stream);
 }
 
 int b200vec_select_count(b200vec_ctx *ctx, const float *data_dev, int64_t n, int positive_only,
@@ -842,10 +883,11 @@ int b200vec_select_begin(b200vec_ctx *ctx, const float *data_dev, int64_t n, int
     B2_CUDA(cudaMemsetAsync(ctx->top_hist, 0, bytes, st));
     if (n > 0) {
         long long grid = (n / 4 + kSelThreads - 1) / kSelThreads + 1;
-        const long long cap = (long long)ctx->sm_count * 4;
+        const long long cap = (long long)ctx->sm_count * 6;         // 6 x 32 KB histograms per SM
         if (grid > cap) grid = cap;
-        sel_top_kernel<<<(unsigned)grid, kSelThreads, 0, st>>>(data_dev, n, use_abs ? 1 : 0, ctx->top_hist,
-                                                               reinterpret_cast<unsigned long long *>(ctx->top_hist + kTopBins));
+        unsigned long long *pz = reinterpret_cast<unsigned long long *>(ctx->top_hist + kTopBins);
+        if (use_abs) sel_top_kernel<true><<<(unsigned)grid, kSelThreads, 0, st>>>(data_dev, n, ctx->top_hist, pz);
+        else sel_top_kernel<false><<<(unsigned)grid, kSelThreads, 0, st>>>(data_dev, n, ctx->top_hist, pz);
         B2_CUDA(cudaGetLastError());
     }
     B2_CUDA(cudaMemcpyAsync(ctx->pinned, ctx->top_hist, bytes, cudaMemcpyDeviceToHost, st));
@@ -900,8 +942,8 @@ int b200vec_select_finish(b200vec_ctx *ctx, const float *data_dev, int64_t n, co
     if (sel.n == 0) return 0;
     for (int i = 1; i < sel.n; ++i)                                   // ascending bins = ascending values
         for (int j = i; j > 0 && sel.bin[j - 1] > sel.bin[j]; --j) { const unsigned t = sel.bin[j]; sel.bin[j] = sel.bin[j - 1]; sel.bin[j - 1] = t; }
-    unsigned long long pop = 0, before[B200VEC_MAX_RANKS];
-    for (int i = 0; i < sel.n; ++i) { before[i] = pop; pop += ts.hist[sel.bin[i]]; }
+    unsigned long long pop = 0;
+    for (int i = 0; i < sel.n; ++i) pop += ts.hist[sel.bin[i]];
     int64_t sub_ranks[B200VEC_MAX_RANKS];
     int sub_of[B200VEC_MAX_RANKS], n_sub = 0;
     const unsigned long long cap_max = (unsigned long long)(n / 8 > (1 << 20) ? n / 8 : (1 << 20));
@@ -911,19 +953,48 @@ int b200vec_select_finish(b200vec_ctx *ctx, const float *data_dev, int64_t n, co
             B2_CUDA(cudaStreamSynchronize(st));
             if (ensure_scratch(ctx->cand, (size_t)(pop + pop / 4 + 1024) * sizeof(float))) return 1;
         }
-        unsigned long long *cnt = reinterpret_cast<unsigned long long *>(ctx->top_hist + kTopBins) + 1;
-        B2_CUDA(cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), st));
-        const unsigned grid = (unsigned)(ctx->sm_count * 8);
-        sel_compact_kernel<<<grid, kSelThreads, 0, st>>>(data_dev, n, ts.use_abs, sel, (float *)ctx->cand.ptr, pop, cnt);
-        B2_CUDA(cudaGetLastError());
+        // The compaction pass also counts the candidates' key bits 18..10 into the level-2 histograms of the exact
+        // select, so the select starts there: rank r enters with its 11-bit prefix (bin >> 2) and its position among
+        // the candidates that share that prefix (the selected bins below its own + its position inside its bin).
+        SelState init;
+        memset(&init, 0, sizeof(init));
         for (int r = 0; r < n_ranks; ++r) {
             if (bin_of[r] < 0) continue;
-            int i = 0;
-            while (sel.bin[i] != (unsigned)bin_of[r]) ++i;
-            sub_ranks[n_sub] = (int64_t)(before[i] + resid[r]); sub_of[n_sub++] = r;
+            const unsigned int p11 = (unsigned)bin_of[r] >> 2;
+            unsigned long long want = resid[r];
+            for (int i = 0; i < sel.n; ++i)
+                if ((sel.bin[i] >> 2) == p11 && sel.bin[i] < (unsigned)bin_of[r]) want += ts.hist[sel.bin[i]];
+            init.prefix[n_sub] = p11; init.resid[n_sub] = want; sub_of[n_sub++] = r;
         }
-        if (run_select(ctx, (const float *)ctx->cand.ptr, (long long)pop, 0, sub_ranks, n_sub, st, &state)) return 1;
-        B2_REQUIRE(state.count == pop, "candidate count differs from the histogram (array changed since b200vec_select_begin?)");
+        init.n_ranks = n_sub; init.count = pop;
+        for (int i = 0; i < sel.n; ++i) {                             // hist2[slot]: the first rank with the bin's prefix owns it
+            sel.slot[i] = 0;
+            for (int q = 0; q < n_sub; ++q)
+                if (init.prefix[q] == (sel.bin[i] >> 2)) { sel.slot[i] = q; break; }
+        }
+        B2_CUDA(cudaMemsetAsync(ctx->hist, 0, sizeof(unsigned int) * kHistWords, st));
+        sel_init<<<1, 1, 0, st>>>(ctx->hist, init);
+        unsigned long long *cnt = reinterpret_cast<unsigned long long *>(ctx->top_hist + kTopBins) + 1;
+        B2_CUDA(cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), st));
+        const unsigned grid = (unsigned)(ctx->sm_count * 4);
+        if (ts.use_abs) sel_compact_kernel<true><<<grid, kSelThreads, 0, st>>>(data_dev, n, sel, (float *)ctx->cand.ptr, pop, cnt, ctx->hist);
+        else sel_compact_kernel<false><<<grid, kSelThreads, 0, st>>>(data_dev, n, sel, (float *)ctx->cand.ptr, pop, cnt, ctx->hist);
+        B2_CUDA(cudaGetLastError());
+        long long blocks = ((long long)pop / 4 + kPickThreads * kSelUnroll - 1) / (kPickThreads * kSelUnroll);
+        if (blocks > ctx->sm_count) blocks = ctx->sm_count;
+        if (blocks < 1) blocks = 1;
+        const float *cand = (const float *)ctx->cand.ptr;
+        long long pop_ll = (long long)pop;
+        void *kargs[] = {(void *)&cand, (void *)&pop_ll, (void *)&ctx->hist};
+        B2_CUDA(cudaLaunchCooperativeKernel((const void *)sel_cand_kernel, dim3((unsigned)blocks), dim3(kPickThreads),
+                                            kargs, (size_t)n_sub * kBins3 * sizeof(unsigned int), st));
+        B2_CUDA(cudaMemcpyAsync(ctx->pinned, ctx->hist + kStateOff, sizeof(SelState), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaMemcpyAsync((char *)ctx->pinned + 1024, cnt, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaStreamSynchronize(st));
+        memcpy(&state, ctx->pinned, sizeof(SelState));
+        unsigned long long got = 0;
+        memcpy(&got, (char *)ctx->pinned + 1024, sizeof(got));
+        B2_REQUIRE(got == pop, "candidate count differs from the histogram (array changed since b200vec_select_begin?)");
     } else {                                                          // a heavily repeated value: 3-level select on the whole array
         for (int r = 0; r < n_ranks; ++r) {
             if (bin_of[r] < 0) continue;

@@ -364,10 +364,16 @@ class Engine:
         v = self.select_finish(flat, ranks)
         floor_ = H.lerp(v[6], v[7], g0) if n_pos > 0 else 1e-12
         floor_ = max(floor_, 1e-12)
-        db = self.db(flat, floor_).view(base.shape)
+        db = torch.empty_like(flat)
+        vin = (C.c_float * 6)(*[float(x) for x in v[:6]])
+        vout = (C.c_float * 6)()
+        check(self.lib.b200vec_db_values(self._ctx, self._ptr(flat), n, float(floor_), self._ptr(db), vin, 6, vout,
+                                         self._stream()))
+        self.launches += 1
+        db = db.view(base.shape)
         if transposed:
             db = db.t()
-        six = self.db(torch.from_numpy(v[:6].copy()).to(self.device), floor_).cpu().numpy()
+        six = np.asarray(list(vout), dtype=np.float32)
         vmin, vmax = H.lerp(six[0], six[1], g1), H.lerp(six[2], six[3], g2)
         vmin, vmax = H.colour_limits(vmin, vmax, six[4], six[5], max_dynamic_range)
         return db, vmin, vmax
