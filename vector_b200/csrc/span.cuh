@@ -113,6 +113,8 @@ __device__ __forceinline__ bool sp_build_half(const SpanArgs &a, const PlaceDesc
     return live;
 }
 
+// (Measured: capping registers for 4 or 5 CTAs per SM instead of 3, or two staging blocks per warp, does not help —
+// 102 -> 111 / 118 us at cfg2 store-only — although the warps mostly wait on the L2 gather.)
 template <bool BATCH>
 __global__ void __launch_bounds__(kSpThreads)
 span_kernel(const __grid_constant__ SpanArgs a) {
@@ -130,13 +132,14 @@ span_kernel(const __grid_constant__ SpanArgs a) {
 
     if (a.mode == B200VEC_BUILD_MAXONLY || a.mode == kSpNorm) {
         // ---------------------------------------------------------------- pass A: max |v|^2 per vector, no stores
-        // every warp takes one contiguous run of the list: consecutive spans mostly belong to one vector
-        const long long per = (a.n_spans + nw - 1) / nw;
-        const long long u1 = (gw + 1) * per < a.n_spans ? (gw + 1) * per : a.n_spans;
+        // The list is sorted by vector and the warps walk it side by side (warp w takes spans w, w + nw, ...): at
+        // any moment the whole GPU works on a handful of vectors, whose packets (3 x 449 KB each) stay in L2 —
+        // a batch's bank is far larger than the L2 (582 shifted packets = 261 MB at cfg5), and one contiguous
+        // run per warp spread the warps over all vectors at once (2.1 GB of DRAM reads per launch).
         double tmax = 0.0;                                   // running max of |v|^2 for vector cur_v (exact products in fp64)
         float fthr = 0.0f;                                   // fp32 pre-filter threshold
         int cur_v = -1;
-        for (long long u = gw * per; u < u1; ++u) {
+        for (long long u = gw; u < a.n_spans; u += nw) {
             const MaxSpan sp = a.spans[u];
             const int v = BATCH ? sp.vec : 0;
             if (v != cur_v) {
@@ -196,6 +199,8 @@ span_kernel(const __grid_constant__ SpanArgs a) {
     const long long n_items = ipv * a.n_vec;
     const bool scaled = a.mode == B200VEC_BUILD_SCALE || a.mode == kSpNorm;
     unsigned next = 0;
+    float scl = 1.0f;
+    int scl_v = -1;
     if (lane == 0) next = atomicAdd(a.ctr, 1u);
     for (;;) {
         const long long c = __shfl_sync(0xffffffffu, next, 0);
@@ -204,10 +209,10 @@ span_kernel(const __grid_constant__ SpanArgs a) {
         const int v = BATCH ? (int)(c / ipv) : 0;
         const long long h0 = (BATCH ? c - (long long)v * ipv : c) * kSpChunk;     // first half of the item
         const int nh = (int)(halves - h0 < kSpChunk ? halves - h0 : kSpChunk);
-        float scl = 1.0f;
-        if (scaled) {
+        if (scaled && v != scl_v) {                          // once per vector, not per item: an L2 round trip + fp64 sqrt
             const double m2 = __longlong_as_double((long long)__ldcg(a.maxsq + v));
-            if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);     // numpy's complex64 / float32: multiply by the fp32 reciprocal
+            scl = m2 > 0.0 ? 1.0f / (float)sqrt(m2) : 1.0f;  // numpy's complex64 / float32: multiply by the fp32 reciprocal
+            scl_v = v;
         }
         const PlaceDesc *dv = BATCH ? a.gdesc + (long long)v * a.pk_stride : nullptr;
         const int np = BATCH ? a.gnp[v] : a.place.np;
