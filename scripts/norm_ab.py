@@ -18,7 +18,18 @@ spec = eng.alloc_spectrogram(1024, nf, frame_major=True)
 KEYS = ("B200VEC_WF_ZW", "B200VEC_WF_TF", "B200VEC_WF_CHUNK", "B200VEC_WF_BULK", "B200VEC_WF_TAIL")
 
 
+MODE = os.environ.get("AB_MODE", "norm")          # norm: the one-launch step; scale: the max is given (no max pass, no grid barrier)
+if MODE == "scale":
+    from vector_b200._lib import BUILD_SCALE
+    _, _, _m = vdist.build_stft_slab(eng, rows, plan, True, None, fs=FS, out_vec=vec, out_spec=spec)
+    descs, nd = eng.make_descs(rows)
+
+
 def run():
+    if MODE == "scale":
+        eng.build_stft1024(descs, nd, plan.lo, plan.hi, vec, BUILD_SCALE, plan.frame_lo, nf, spec, window="hann", fs=FS,
+                           scaling="density")
+        return vec, spec, eng._maxsq
     return vdist.build_stft_slab(eng, rows, plan, True, None, fs=FS, out_vec=vec, out_spec=spec)
 
 

@@ -1,7 +1,7 @@
 """Timing of every kernel family of the path OTHER than the bench step, at the BASELINE size (cfg2,
 56 M samples / 109 374 x 1024 spectrogram): algorithmic bytes / device time, fraction of the measured
 HBM peak.  CUDA events on the current stream, 3 warm-ups, median of 9.  One JSON object per line."""
-import json, os, sys
+import json, os, sys, contextlib
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from vector_b200 import api, generate, synth
@@ -21,27 +21,40 @@ rows = generate.placement_rows(cfgs, info, N, FS)
 
 
 def timed(name, fn, alg_bytes, note=""):
+    """Device time per call.  Calls that only launch kernels are captured in a CUDA graph (10 calls per replay) so that
+    launch gaps do not count; calls that synchronise (host read-backs) are timed eagerly, host round trips included."""
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
+    how, per = "graph replay of 10 calls", 10
+    try:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(per):
+                fn()
+        run = g.replay
+    except Exception:
+        torch.cuda.synchronize()
+        how, per, run = "eager, host round trips included", 1, fn
+    run(); torch.cuda.synchronize()
     ts = []
     for _ in range(9):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(); fn(); b.record(); b.synchronize()
-        ts.append(a.elapsed_time(b))
+        a.record(); run(); b.record(); b.synchronize()
+        ts.append(a.elapsed_time(b) / per)
     ts.sort()
     ms = ts[len(ts) // 2]
     gbs = alg_bytes / ms / 1e6
     print(json.dumps({"kernel": name, "ms": round(ms, 4), "alg_bytes": alg_bytes, "GBps": round(gbs, 1),
-                      "frac_of_measured_peak": round(gbs / PEAK, 3), "note": note}), flush=True)
+                      "frac_of_measured_peak": round(gbs / PEAK, 3), "timing": how, "note": note}), flush=True)
 
 
 vec = torch.empty(N, dtype=torch.complex64, device=eng.device)
 descs, nd = eng.make_descs(rows)
 timed("K2 place_kernel, store only (a6)", lambda: eng.build_pass(descs, nd, 0, N, vec, BUILD_STORE), 8 * N,
       "8 B/Sa written, nothing read")
-timed("K2+K3 two-pass normalised build (a6+a7)", lambda: eng.build_vector(rows, N, True, out=vec), 8 * N,
-      "pass A over one common period + head/tail, pass B recompute + store; includes host descriptor upload")
+timed("K2+K3 normalised build, one launch (a6+a7)", lambda: eng.build_vector(rows, N, True, out=vec), 8 * N,
+      "max pass over the planned spans + grid barrier + scaled store pass (b200vec_build_norm)")
 v, _ = eng.build_vector(rows, N, True, out=vec)
 
 nf = (N - 1024) // 512 + 1
@@ -53,10 +66,15 @@ timed("K4 stft1024 tile kernel, C-order rows (a9)",
       lambda: eng.stft(v, "hann", 1024, 512, 1024, FS, out=spec_c), 8 * N + 4 * 1024 * nf, "same bytes, [1024, frames] memory")
 del spec_c
 
-f, t, S = api.create_spectrogram_device(v, FS, time_resolution_us=1, engine=eng)
+def preview():
+    with contextlib.redirect_stdout(sys.stderr):          # the reference's own progress prints (utils.py:186-200)
+        return api.create_spectrogram_device(v, FS, time_resolution_us=1, engine=eng)
+
+
+f, t, S = preview()
 prev_bytes = 32 * (N // 56) + 4 * S.numel()
 timed("K4 generic, create_spectrogram preview (a8: decimate x56, hann 512/412, nfft 1024)",
-      lambda: api.create_spectrogram_device(v, FS, time_resolution_us=1, engine=eng), prev_bytes,
+      preview, prev_bytes,
       f"32 B sector per decimated sample + {tuple(S.shape)} float32 out; includes the all-zero flag read-back")
 
 timed("K5 normalize_spectrogram on the preview (a10)", lambda: eng.normalize_spectrogram(S, 5, 95, 25),
