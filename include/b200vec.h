@@ -302,6 +302,11 @@ int b200vec_split_planes(b200vec_ctx *ctx, const void *in_dev, int64_t n, float 
  *                     Element strides are explicit so both spectrogram layouts work; not in place. */
 int b200vec_box_energy(b200vec_ctx *ctx, const void *in_dev, int64_t n, int window, double *smoothed_out_dev,
                        double *max_out_dev, void *stream);
+/* Exact order statistics of a float64 device array: values_host[i] = element at 0-based position ranks_host[i]
+ * of the ascending sort (n_ranks <= 4) — np.median of the smoothed energies' first tenth (utils.py:818) takes
+ * the two middle ones.  One cooperative launch (radix select on 64-bit keys).  Synchronises the stream. */
+int b200vec_select_f64(b200vec_ctx *ctx, const double *data_dev, int64_t n, const int64_t *ranks_host, int n_ranks,
+                       double *values_host, void *stream);
 int b200vec_threshold_bounds(b200vec_ctx *ctx, const double *smoothed_dev, int64_t n, double threshold,
                              int64_t *first_last_host, void *stream);
 int b200vec_median2_rows(b200vec_ctx *ctx, const float *in_dev, int64_t rows, int64_t cols, int64_t in_row_stride,

@@ -514,6 +514,21 @@ def test_select_is_exact(eng):
             assert eng.percentile(d, q) == np.percentile(a, q)
 
 
+def test_select_f64_is_exact(eng):
+    """b200vec_select_f64 (np.median of detect_packet_bounds' smoothed energies, utils.py:818): exact order
+    statistics of float64 data — duplicates, negatives, values that differ only in their lowest bits."""
+    rng = np.random.default_rng(12)
+    for n in (1, 2, 33, 5000, 400_001):
+        a = rng.standard_normal(n) * 10.0 ** rng.integers(-12, 3, n)
+        a[rng.integers(0, n, n // 4)] = 0.0
+        a[rng.integers(0, n, n // 5)] = 1.0 + np.finfo(np.float64).eps * rng.integers(0, 4, n // 5)
+        srt = np.sort(a)
+        d = torch.from_numpy(a).cuda()
+        for ranks in ([0], [n - 1], [n // 2], sorted({max(0, n // 2 - 1), n // 2}), sorted({0, n // 3, n // 2, n - 1})):
+            got = eng.select_f64(d, ranks)
+            assert got == [float(srt[r]) for r in ranks], (n, ranks, got)
+
+
 @pytest.mark.parametrize("name", ["wf_2p5ms_shift_norm", "cfg1_100ms"])
 def test_normalize_spectrogram_matches_oracle(eng, name):
     import vector_b200 as vb

@@ -453,8 +453,8 @@ def detect_packet_bounds(signal, sample_rate, threshold_ratio=0.2):
     ratio * (peak - noise) with noise = median of the first tenth, first / last sample above it;
     (0, len(signal)) when nothing is above.  `signal`: numpy array or complex64 CUDA tensor.
     Smoothing, peak and the index search run on the device (K8/K9); the median is an exact order
-    statistic of the device array (sorted there), the two scalars are combined on the host in double
-    precision exactly like the reference's numpy scalars."""
+    statistic of the device array (radix select on 64-bit keys, one launch), the two scalars are combined
+    on the host in double precision exactly like the reference's numpy scalars."""
     eng = get_engine(signal.device) if isinstance(signal, torch.Tensor) and signal.is_cuda else get_engine()
     if isinstance(signal, torch.Tensor):
         dev = signal.reshape(-1).to(device=eng.device, dtype=torch.complex64)
@@ -475,9 +475,12 @@ def detect_packet_bounds(signal, sample_rate, threshold_ratio=0.2):
         dev = pad
     smoothed, max_en = eng.box_energy(dev, window)
     head = smoothed[: max(1, smoothed.numel() // 10)]         # len(smoothed) = max(n, window)
-    srt, _ = torch.sort(head)
-    m = srt.numel()
-    noise = float(srt[m // 2]) if m % 2 else float((srt[m // 2 - 1] + srt[m // 2]) / 2)     # np.median
+    m = head.numel()
+    if m % 2:                                                 # np.median: exact order statistics (b200vec_select_f64)
+        noise = eng.select_f64(head, [m // 2])[0]
+    else:
+        lo_v, hi_v = eng.select_f64(head, [m // 2 - 1, m // 2])
+        noise = float((np.float64(lo_v) + np.float64(hi_v)) / 2)
     max_en = float(max_en)
     threshold = noise + threshold_ratio * (max_en - noise)
     first, last = eng.threshold_bounds(smoothed, threshold)

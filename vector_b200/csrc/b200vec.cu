@@ -193,6 +193,7 @@ int b200vec_destroy(b200vec_ctx *ctx) {
     if (ctx->batch.bank.ptr) cudaFree(ctx->batch.bank.ptr);
     if (ctx->batch.tables.ptr) cudaFree(ctx->batch.tables.ptr);
     if (ctx->batch.pin) cudaFreeHost(ctx->batch.pin);
+    if (ctx->sel64.ptr) cudaFree(ctx->sel64.ptr);
     for (SpanCache *c : {&ctx->batch.spans, &ctx->max_spans}) {
         if (c->dev.ptr) cudaFree(c->dev.ptr);
         if (c->pin) cudaFreeHost(c->pin);
@@ -1107,6 +1108,39 @@ int b200vec_box_energy(b200vec_ctx *ctx, const void *in_dev, int64_t n, int wind
     box_energy_kernel<<<(unsigned)grid, kBoxThreads, 0, st>>>((const float2 *)in_dev, n, window, smoothed_out_dev,
                                                               reinterpret_cast<unsigned long long *>(max_out_dev));
     B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int b200vec_select_f64(b200vec_ctx *ctx, const double *data_dev, int64_t n, const int64_t *ranks_host, int n_ranks,
+                       double *values_host, void *stream) {
+    B2_REQUIRE(ctx && data_dev && ranks_host && values_host, "NULL argument");
+    B2_REQUIRE(n >= 1 && n_ranks >= 1 && n_ranks <= kSel64MaxRanks, "n >= 1 and 1 <= n_ranks <= 4");
+    for (int r = 0; r < n_ranks; ++r) B2_REQUIRE(ranks_host[r] >= 0 && ranks_host[r] < n, "rank outside the array");
+    DeviceGuard g(ctx->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t bytes = 256 + 2 * kSel64MaxRanks * 2048 * sizeof(unsigned int);
+    if (ensure_scratch(ctx->sel64, bytes)) return 1;
+    Sel64State init;
+    memset(&init, 0, sizeof(init));
+    init.n_ranks = n_ranks;
+    for (int r = 0; r < n_ranks; ++r) init.resid[r] = (unsigned long long)ranks_host[r];
+    static_assert(sizeof(Sel64State) <= 256, "state block");
+    B2_CUDA(cudaMemsetAsync(ctx->sel64.ptr, 0, bytes, st));
+    memcpy(ctx->pinned, &init, sizeof(init));
+    B2_CUDA(cudaMemcpyAsync(ctx->sel64.ptr, ctx->pinned, sizeof(init), cudaMemcpyHostToDevice, st));
+    long long blocks = (n + kSel64Threads * 8 - 1) / (kSel64Threads * 8);
+    if (blocks > ctx->sm_count) blocks = ctx->sm_count;
+    void *scratch = ctx->sel64.ptr;
+    void *kargs[] = {(void *)&data_dev, (void *)&n, (void *)&scratch};
+    B2_CUDA(cudaLaunchCooperativeKernel((const void *)sel64_kernel, dim3((unsigned)blocks), dim3(kSel64Threads), kargs, 0, st));
+    B2_CUDA(cudaMemcpyAsync(ctx->pinned, ctx->sel64.ptr, sizeof(init), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    memcpy(&init, ctx->pinned, sizeof(init));
+    for (int r = 0; r < n_ranks; ++r) {
+        const unsigned long long k = init.result[r];
+        const unsigned long long u = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
+        memcpy(&values_host[r], &u, sizeof(double));
+    }
     return 0;
 }
 

@@ -115,6 +115,7 @@ struct b200vec_ctx {
     unsigned int *sp_ctr = nullptr;       // work-item counter / grid barrier of the span kernel (span.cuh)
     b200vec::BatchState batch;            // prepared scenario batch
     b200vec::SpanCache max_spans;         // must-evaluate spans of the last normalised single-vector build
+    b200vec::Scratch sel64;               // state + histograms of the float64 select (packet.cuh)
     unsigned int *top_hist = nullptr;     // [kTopBins] u32 + one u64 (+0 count) + one u64 (candidate count)
     b200vec::Scratch cand;                // candidate array of the fast select
     b200vec::TopState top;

@@ -479,6 +479,17 @@ def _box_energy(self, x, window):
     return out, mx
 
 
+def _select_f64(self, x, ranks):
+    """Exact values at `ranks` of the ascending sort of a float64 CUDA tensor (b200vec_select_f64)."""
+    x = x.contiguous().view(-1)
+    ranks = [int(r) for r in ranks]
+    arr = (C.c_int64 * len(ranks))(*ranks)
+    vals = (C.c_double * len(ranks))()
+    check(self.lib.b200vec_select_f64(self._ctx, self._ptr(x), x.numel(), arr, len(ranks), vals, self._stream()))
+    self.launches += 1
+    return [float(v) for v in vals]
+
+
 def _threshold_bounds(self, smoothed, threshold):
     """(first, last) index with smoothed >= threshold; (n, -1) when none — b200vec_threshold_bounds."""
     res = (C.c_int64 * 2)()
@@ -499,6 +510,7 @@ def _median2_rows(self, s):
 
 Engine.box_energy = _box_energy
 Engine.threshold_bounds = _threshold_bounds
+Engine.select_f64 = _select_f64
 Engine.median2_rows = _median2_rows
 
 
