@@ -268,6 +268,16 @@ int b200vec_select_begin(b200vec_ctx *ctx, const float *data_dev, int64_t n, int
 int b200vec_select_finish(b200vec_ctx *ctx, const float *data_dev, int64_t n, const int64_t *ranks_host,
                           int n_ranks, float *values_host, void *stream);
 
+/* normalize_spectrogram's device work in ONE call (utils.py:356-373, called with 5 / 95 / 25 by plot_spectrogram,
+ * utils.py:431): select_begin, numpy's float32 percentile index arithmetic on the host (npquant.h), select_finish,
+ * the floor, the dB map.  db_out_dev[i] = 10*log10(|s[i]| + floor); values_host[0] = floor,
+ * [1..6] = the dB-image values at the ranks (low percentile: lower / upper neighbour; high percentile: lower /
+ * upper neighbour; minimum; maximum), [7], [8] = the float32 interpolation weights of the two percentiles;
+ * *n_pos_host = number of elements > 0.  The caller finishes with numpy's lerp and utils.py:375-397.  n >= 1.
+ * Synchronises the stream. */
+int b200vec_normalize_db(b200vec_ctx *ctx, const float *s_dev, int64_t n, double low_percentile, double high_percentile,
+                         float *db_out_dev, float *values_host, int64_t *n_pos_host, void *stream);
+
 /* out_dev[i] = in_dev[i * stride], i < ceil(n_in / stride): the naive decimation sig[::factor] of
  * create_spectrogram (utils.py:192-195), made once so that the overlapping preview frames read a compact
  * copy. */

@@ -12,6 +12,7 @@
 #include "wf1024.cuh"
 #include "span.cuh"
 #include "packet.cuh"
+#include "npquant.h"
 #include "select.cuh"
 
 namespace b200vec {
@@ -1004,6 +1005,35 @@ int b200vec_select_finish(b200vec_ctx *ctx, const float *data_dev, int64_t n, co
         if (run_select(ctx, data_dev, n, ts.use_abs ? 2 : 0, sub_ranks, n_sub, st, &state)) return 1;
     }
     for (int i = 0; i < n_sub; ++i) values_host[sub_of[i]] = key2f(state.result[i]);
+    return 0;
+}
+
+int b200vec_normalize_db(b200vec_ctx *ctx, const float *s_dev, int64_t n, double low_percentile, double high_percentile,
+                         float *db_out_dev, float *values_host, int64_t *n_pos_host, void *stream) {
+    B2_REQUIRE(ctx && s_dev && db_out_dev && values_host && n >= 1, "bad arguments");
+    int64_t n_pos = 0;
+    if (b200vec_select_begin(ctx, s_dev, n, 1, &n_pos, stream)) return 1;
+    // numpy's float32 index arithmetic (npquant.h): dB is monotone in |S|, so the low / high percentiles, minimum
+    // and maximum of the dB image and the 5th percentile of the positive elements are eight ranks of the sorted |S|
+    const PctRanks r1 = pct_ranks_f32(n, low_percentile), r2 = pct_ranks_f32(n, high_percentile);
+    PctRanks r0 = {0, 0, 0.0f};
+    int64_t ranks[8] = {r1.lo, r1.hi, r2.lo, r2.hi, 0, n - 1, 0, 0};
+    int nr = 6;
+    if (n_pos > 0) {
+        r0 = pct_ranks_f32(n_pos, 5.0);
+        ranks[6] = n - n_pos + r0.lo; ranks[7] = n - n_pos + r0.hi;      // the positive elements are the top n_pos of |S|
+        nr = 8;
+    }
+    float v[8] = {0};
+    if (b200vec_select_finish(ctx, s_dev, n, ranks, nr, v, stream)) return 1;
+    float floor_v = n_pos > 0 ? lerp_f32(v[6], v[7], r0.gamma) : (float)1e-12;
+    if ((float)1e-12 > floor_v) floor_v = (float)1e-12;                   // max(floor, 1e-12), utils.py:366
+    float six[6];
+    if (b200vec_db_values(ctx, s_dev, n, floor_v, db_out_dev, v, 6, six, stream)) return 1;
+    values_host[0] = floor_v;
+    for (int i = 0; i < 6; ++i) values_host[1 + i] = six[i];
+    values_host[7] = r1.gamma; values_host[8] = r2.gamma;
+    if (n_pos_host) *n_pos_host = n_pos;
     return 0;
 }
 

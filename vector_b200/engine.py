@@ -354,26 +354,17 @@ class Engine:
         n = flat.numel()
         if n == 0:
             return torch.empty_like(s), 0, 0
-        n_pos = self.select_begin(flat, use_abs=True)
-        lo1, hi1, g1 = H.percentile_ranks(n, low_percentile, np.float32)
-        lo2, hi2, g2 = H.percentile_ranks(n, high_percentile, np.float32)
-        ranks = [lo1, hi1, lo2, hi2, 0, n - 1]
-        if n_pos > 0:
-            lo0, hi0, g0 = H.percentile_ranks(n_pos, 5, np.float32)
-            ranks += [n - n_pos + lo0, n - n_pos + hi0]          # the positive elements are the top n_pos of |S|
-        v = self.select_finish(flat, ranks)
-        floor_ = H.lerp(v[6], v[7], g0) if n_pos > 0 else 1e-12
-        floor_ = max(floor_, 1e-12)
         db = torch.empty_like(flat)
-        vin = (C.c_float * 6)(*[float(x) for x in v[:6]])
-        vout = (C.c_float * 6)()
-        check(self.lib.b200vec_db_values(self._ctx, self._ptr(flat), n, float(floor_), self._ptr(db), vin, 6, vout,
-                                         self._stream()))
-        self.launches += 1
+        vals = (C.c_float * 9)()
+        n_pos = C.c_int64()
+        check(self.lib.b200vec_normalize_db(self._ctx, self._ptr(flat), n, float(low_percentile), float(high_percentile),
+                                            self._ptr(db), vals, C.byref(n_pos), self._stream()))
+        self.launches += 5
+        out = np.asarray(list(vals), dtype=np.float32)
+        six, g1, g2 = out[1:7], out[7], out[8]
         db = db.view(base.shape)
         if transposed:
             db = db.t()
-        six = np.asarray(list(vout), dtype=np.float32)
         vmin, vmax = H.lerp(six[0], six[1], g1), H.lerp(six[2], six[3], g2)
         vmin, vmax = H.colour_limits(vmin, vmax, six[4], six[5], max_dynamic_range)
         return db, vmin, vmax
