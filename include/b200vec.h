@@ -43,10 +43,11 @@ typedef struct b200vec_pkt_desc {
     int64_t period;    /* > 0 */
     int64_t count;     /* K_p, may be 0 */
     int32_t slot;      /* bank slot holding the committed (resampled/shifted) packet */
-    int32_t reserved;  /* bit 0 (optional hint for the in-kernel max of ..._fm_norm[_peer]): the caller vouches that
-                        * at least one instance of this packet lies in the vector with no other instance over any
-                        * of its samples; max |y|^2 of the whole packet (kept by the bank) is then attained by the
-                        * vector and pass A skips spans lying inside exactly one instance of it.  0 = no hint. */
+    int32_t reserved;  /* bit 0 (optional hint for the max pass of the normalised builds): the caller vouches that
+                        * every sample of this packet appears unsummed somewhere in the vector (for every packet-local
+                        * index some instance has no other instance over that sample — e.g. one free-standing instance);
+                        * max |y|^2 of the whole packet (kept by the bank) is then attained by the vector, and the max
+                        * pass skips every sample lying under exactly one instance of it.  0 = no hint. */
 } b200vec_pkt_desc;
 
 enum b200vec_build_mode {

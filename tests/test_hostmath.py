@@ -274,14 +274,17 @@ def test_save_vector_flattens_and_casts(tmp_path):
 
 # ------------------------------------------------------------------------------ free-instance hint
 def _brute_free_flags(rows, lengths, total):
-    inst = [(s + k * p, s + k * p + n, i) for i, ((s, p, c, _), n) in enumerate(zip(rows, lengths)) for k in range(c)]
-    flags = [False] * len(rows)
-    for a0, a1, i in inst:
-        if a1 > total:
-            continue
-        if all(not (b0 < a1 and b1 > a0) for b0, b1, j in inst if (b0, b1, j) != (a0, a1, i)) and \
-           sum(1 for x in inst if x == (a0, a1, i)) == 1:
-            flags[i] = True
+    """Every packet-local sample unsummed somewhere: coverage counted sample by sample."""
+    cov = np.zeros(total, np.int32)
+    for (s, p, c, _), n in zip(rows, lengths):
+        for k in range(c):
+            cov[s + k * p:s + k * p + n] += 1
+    flags = []
+    for (s, p, c, _), n in zip(rows, lengths):
+        seen = np.zeros(n, bool)
+        for k in range(c):
+            seen |= cov[s + k * p:s + k * p + n] == 1
+        flags.append(bool(c > 0 and seen.all()))
     return flags
 
 
@@ -300,5 +303,7 @@ def test_free_instance_flags_match_brute_force():
         assert H.free_instance_flags(rows, lengths, total) == _brute_free_flags(rows, lengths, total)
     assert H.free_instance_flags([(0, 10, 0, 0)], [5], 100) == [False]
     assert H.free_instance_flags([(0, 10, 3, 0)], [5], 100) == [True]
-    assert H.free_instance_flags([(0, 4, 3, 0)], [5], 100) == [False]                     # every instance overlaps a neighbour
+    assert H.free_instance_flags([(0, 4, 3, 0)], [5], 100) == [True]                      # neighbours overlap by one sample: head free in the first, tail in the last
+    assert H.free_instance_flags([(0, 2, 3, 0)], [5], 100) == [False]                     # sample 2 is always under a neighbour
+    assert H.free_instance_flags([(0, 10, 3, 0), (2, 10, 3, 1)], [5, 5], 100) == [False, False]
     assert H.free_instance_flags([(0, 10, 3, 0)], [5], 100, max_instances=2) == [False]   # conservative cap

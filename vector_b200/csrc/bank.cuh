@@ -11,6 +11,22 @@ namespace b200vec {
 //   y[n] = complex64( complex128(x[n]) * (cos phase + j sin phase) )   (utils.py:126-127)
 // Products and sums are kept un-fused (__dmul_rn/__dadd_rn) like numpy's complex128 loop.
 // ---------------------------------------------------------------------------------------
+// sin / cos of a phase of any size without libdevice's Payne-Hanek path (taken above ~1.06e5 rad: a 20 MHz shift
+// reaches 1.26e5 rad at the end of a 1 ms packet, and one slow lane stalls its warp): phases past 1e5 rad are
+// first reduced by the nearest multiple of 2*pi with the product kept exact inside FMAs (2*pi = C1 + C2 + C3,
+// |k| < 2^33: error below 1e-15 rad, far under what the single rounding to float32 of utils.py:127 can see);
+// smaller phases go to sincos() unchanged, bit for bit as before.
+__device__ __forceinline__ void sincos_phase(double ph, double *s, double *c) {
+    if (fabs(ph) > 1.0e5 && fabs(ph) < 5.0e10) {
+        const double k = rint(ph * 0.15915494309189535);              // 1 / (2*pi)
+        double r = fma(-k, 6.2831853071795862, ph);                   // 2*pi rounded to double
+        r = fma(-k, 2.4492935982947064e-16, r);                       // 2*pi - C1
+        r = fma(-k, -5.9895396194366790e-33, r);                      // 2*pi - C1 - C2
+        ph = r;
+    }
+    sincos(ph, s, c);
+}
+
 __global__ void __launch_bounds__(256)
 shift_commit_kernel(const float2 *__restrict__ raw, long long len, double w, double fs,
                     int do_shift, float2 *__restrict__ a, float2 *__restrict__ b) {
@@ -21,7 +37,7 @@ shift_commit_kernel(const float2 *__restrict__ raw, long long len, double w, dou
         const double t = (double)n / fs;
         const double ph = __dmul_rn(w, t);
         double s, c;
-        sincos(ph, &s, &c);
+        sincos_phase(ph, &s, &c);
         const double xr = (double)y.x, xi = (double)y.y;
         const double re = __dsub_rn(__dmul_rn(xr, c), __dmul_rn(xi, s));
         const double im = __dadd_rn(__dmul_rn(xr, s), __dmul_rn(xi, c));

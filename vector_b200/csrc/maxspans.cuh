@@ -6,9 +6,9 @@
 // tail).  Inside those ranges most samples need no evaluation at all:
 //   * where NO instance lies, v = 0;
 //   * where exactly ONE instance lies, |v| = |y_p[n]| <= max |y_p|, and if the caller vouches
-//     (b200vec_pkt_desc.reserved bit 0, hostmath.free_instance_flags) that some instance of packet p stands
-//     free in the vector, max |y_p| is attained by the vector itself: it enters the reduction through the
-//     bank's per-slot packet max (PlaceDesc::pmax) and these samples add nothing.
+//     (b200vec_pkt_desc.reserved bit 0, hostmath.free_instance_flags) that every sample of packet p appears
+//     unsummed somewhere in the vector, max |y_p| is attained by the vector itself: it enters the reduction
+//     through the bank's per-slot packet max (PlaceDesc::pmax) and these samples add nothing.
 // What is left — samples under >= 2 instances, or under an instance of an unflagged packet — is found
 // here by one sweep over the sorted instance boundaries and handed to the kernels as a compact list of
 // spans of <= 512 samples: one warp-sized piece of work each, ~1 per warp at the BASELINE config (1 238

@@ -25,10 +25,10 @@ constexpr int kVec = kTile / (2 * kPlaceThreads);   // float4 (= 2 samples) per 
 struct PlaceDesc {
     long long start, period, count;
     int len;
-    int free_inst;                    // the caller vouches that one instance of this packet lies in the vector with no
-                                      // other instance over it (b200vec_pkt_desc::reserved bit 0): max |y|^2 over the
-                                      // whole packet is then attained by the vector, and pass A may skip spans that
-                                      // lie inside exactly one instance of it
+    int free_inst;                    // the caller vouches that every sample of this packet appears unsummed somewhere
+                                      // in the vector (b200vec_pkt_desc::reserved bit 0): max |y|^2 over the whole
+                                      // packet is then attained by the vector, and the max pass skips every sample
+                                      // lying under exactly one instance of it
     const unsigned long long *pmax;   // bits of max |y|^2 (double) over the committed packet (bank, device memory)
     const float2 *a;                  // y[0], 16-byte aligned copy
     const float2 *b;                  // y[0], 8-mod-16 copy

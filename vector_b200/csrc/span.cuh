@@ -26,7 +26,8 @@ namespace b200vec {
 
 constexpr int kSpWarps = 8;
 constexpr int kSpThreads = 32 * kSpWarps;
-constexpr int kSpChunk = 4;                                       // halves per work item
+constexpr int kSpChunk = 4;                                       // halves per work item (single vector)
+constexpr int kSpChunkBatch = 16;                                 // batch: the per-item descriptor fetch (device memory) is amortised over 64 KB
 constexpr int kSpNorm = 3;                                        // SpanArgs::mode: max pass + grid barrier + scale pass
 constexpr size_t kSpSmem = (size_t)kSpWarps * 4096 + 4096;        // per-warp staging blocks + one block of zeros
 
@@ -57,9 +58,15 @@ __device__ __forceinline__ void sp_overlap(const SpanArgs &a, const PlaceDesc *d
                                            int span, int &cnt_l, int &rel0_l) {
     cnt_l = 0; rel0_l = 0;
     if (lane < np) {
-        const PlaceDesc &d = sp_desc<BATCH>(a, dv, lane);
-        const long long start = d.start, period = d.period, count = d.count;
-        const int len = d.len;
+        long long start, period, count;
+        int len;
+        if constexpr (BATCH) {               // read-only path (L1): every warp of an SM reads the same few vectors' descriptors
+            start = __ldg(&dv[lane].start); period = __ldg(&dv[lane].period);        // 56-byte records: 8-byte loads
+            count = __ldg(&dv[lane].count); len = __ldg(&dv[lane].len);
+        } else {
+            const PlaceDesc &d = a.place.d[lane];
+            start = d.start; period = d.period; count = d.count; len = d.len;
+        }
         long long klo = floor_div(s0 - len - start, period) + 1;
         long long khi = floor_div(s0 + span - 1 - start, period);
         if (klo < 0) klo = 0;
@@ -81,10 +88,16 @@ __device__ __forceinline__ bool sp_build_half(const SpanArgs &a, const PlaceDesc
         const int p = __ffs(m) - 1;
         const int cnt = __shfl_sync(0xffffffffu, cnt_l, p);
         const int rel0 = __shfl_sync(0xffffffffu, rel0_l, p);
-        const PlaceDesc &d = sp_desc<BATCH>(a, dv, p);
-        const int len = d.len;
-        const long long period = d.period;
-        const float2 *ya = d.a;
+        int len;
+        long long period;
+        const float2 *ya;
+        if constexpr (BATCH) {
+            len = __ldg(&dv[p].len); period = __ldg(&dv[p].period);
+            ya = reinterpret_cast<const float2 *>(__ldg(reinterpret_cast<const unsigned long long *>(&dv[p].a)));
+        } else {
+            const PlaceDesc &d = a.place.d[p];
+            len = d.len; period = d.period; ya = d.a;
+        }
         long long r64 = (long long)rel0 + off;               // packet index of the half's sample 0 for instance klo + i
         for (int i = 0; i < cnt; ++i, r64 -= period) {
             if (r64 + 512 <= 0) break;                       // this and every later instance start after the half
@@ -140,7 +153,9 @@ span_kernel(const __grid_constant__ SpanArgs a) {
         float fthr = 0.0f;                                   // fp32 pre-filter threshold
         int cur_v = -1;
         for (long long u = gw; u < a.n_spans; u += nw) {
-            const MaxSpan sp = a.spans[u];
+            const int4 sraw = __ldg(reinterpret_cast<const int4 *>(a.spans + u));      // one 16-byte read-only load
+            MaxSpan sp;
+            sp.s0 = (long long)(((unsigned long long)(unsigned)sraw.y << 32) | (unsigned)sraw.x); sp.n = sraw.z; sp.vec = sraw.w;
             const int v = BATCH ? sp.vec : 0;
             if (v != cur_v) {
                 if (cur_v >= 0) {
@@ -150,7 +165,7 @@ span_kernel(const __grid_constant__ SpanArgs a) {
                 cur_v = v; tmax = 0.0; fthr = 0.0f;
             }
             const PlaceDesc *dv = BATCH ? a.gdesc + (long long)v * a.pk_stride : nullptr;
-            const int np = BATCH ? a.gnp[v] : a.place.np;
+            const int np = BATCH ? __ldg(a.gnp + v) : a.place.np;
             int cnt_l, rel0_l;
             sp_overlap<BATCH>(a, dv, np, lane, sp.s0, 512, cnt_l, rel0_l);
             const unsigned active = __ballot_sync(0xffffffffu, cnt_l > 0);
@@ -195,7 +210,8 @@ span_kernel(const __grid_constant__ SpanArgs a) {
     // -------------------------------------------------------------------- pass B: place, scale, store
     const long long n = a.hi - a.lo;
     const long long halves = (n + 511) / 512;
-    const long long ipv = (halves + kSpChunk - 1) / kSpChunk;                 // items per vector
+    constexpr int kChunk = BATCH ? kSpChunkBatch : kSpChunk;
+    const long long ipv = (halves + kChunk - 1) / kChunk;                     // items per vector
     const long long n_items = ipv * a.n_vec;
     const bool scaled = a.mode == B200VEC_BUILD_SCALE || a.mode == kSpNorm;
     unsigned next = 0;
@@ -207,15 +223,15 @@ span_kernel(const __grid_constant__ SpanArgs a) {
         if (c >= n_items) break;
         if (lane == 0) next = atomicAdd(a.ctr, 1u);         // the next item's index arrives while this one is processed
         const int v = BATCH ? (int)(c / ipv) : 0;
-        const long long h0 = (BATCH ? c - (long long)v * ipv : c) * kSpChunk;     // first half of the item
-        const int nh = (int)(halves - h0 < kSpChunk ? halves - h0 : kSpChunk);
+        const long long h0 = (BATCH ? c - (long long)v * ipv : c) * kChunk;       // first half of the item
+        const int nh = (int)(halves - h0 < kChunk ? halves - h0 : kChunk);
         if (scaled && v != scl_v) {                          // once per vector, not per item: an L2 round trip + fp64 sqrt
             const double m2 = __longlong_as_double((long long)__ldcg(a.maxsq + v));
             scl = m2 > 0.0 ? 1.0f / (float)sqrt(m2) : 1.0f;  // numpy's complex64 / float32: multiply by the fp32 reciprocal
             scl_v = v;
         }
         const PlaceDesc *dv = BATCH ? a.gdesc + (long long)v * a.pk_stride : nullptr;
-        const int np = BATCH ? a.gnp[v] : a.place.np;
+        const int np = BATCH ? __ldg(a.gnp + v) : a.place.np;
         int cnt_l, rel0_l;
         sp_overlap<BATCH>(a, dv, np, lane, a.lo + h0 * 512, nh * 512, cnt_l, rel0_l);
         const unsigned active = __ballot_sync(0xffffffffu, cnt_l > 0);
@@ -263,7 +279,8 @@ inline int launch_span(b200vec_ctx *ctx, SpanArgs &a, cudaStream_t st) {
         B2_REQUIRE(occ[batch] > 0, "span_kernel does not fit an SM");
     }
     const long long halves = n > 0 ? (n + 511) / 512 : 0;
-    const long long items = pass_b ? (halves + kSpChunk - 1) / kSpChunk * a.n_vec : 0;
+    const int chunk = batch ? kSpChunkBatch : kSpChunk;
+    const long long items = pass_b ? (halves + chunk - 1) / chunk * a.n_vec : 0;
     const long long units = a.n_spans;
     const long long work = items > units ? items : units;
     const long long cap = (long long)ctx->sm_count * occ[batch];       // one full wave: persistent warps, dynamic items
@@ -307,7 +324,7 @@ batch_shift_kernel(const ShiftJob *__restrict__ jobs, double fs) {
             const double t = (double)n / fs;
             const double ph = __dmul_rn(jb.w, t);
             double s, c;
-            sincos(ph, &s, &c);
+            sincos_phase(ph, &s, &c);
             const double xr = (double)y.x, xi = (double)y.y;
             const double re = __dsub_rn(__dmul_rn(xr, c), __dmul_rn(xi, s));
             const double im = __dadd_rn(__dmul_rn(xr, s), __dmul_rn(xi, c));

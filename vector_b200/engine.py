@@ -379,9 +379,10 @@ class Engine:
         return out
 
     # ------------------------------------------------------------------ scenario batch
-    def batch_prepare(self, scenarios, fs_hz):
-        """scenarios: per vector a list of (start, period, count, src_slot, freq_hz[, free_flag]) — every
-        distinct (src_slot, freq_hz) is shifted once, in one launch (b200vec_batch_prepare)."""
+    @staticmethod
+    def pack_batch(scenarios):
+        """The ctypes tables of b200vec_batch_prepare for `scenarios` (per vector a list of (start, period, count,
+        src_slot, freq_hz[, free_flag])): built once, reusable for every step that re-prepares the same sweep."""
         from ._lib import BatchPkt
         n_pk = sum(len(sc) for sc in scenarios)
         pk = (BatchPkt * max(n_pk, 1))()
@@ -395,11 +396,20 @@ class Engine:
                                  1 if (len(row) > 5 and row[5]) else 0, float(freq))
                 i += 1
         first[len(scenarios)] = i
-        check(self.lib.b200vec_batch_prepare(self._ctx, pk, first, len(scenarios), float(fs_hz), self._stream()))
+        jobs = len({(int(r[3]), float(r[4])) for sc in scenarios for r in sc})
+        return {"pk": pk, "first": first, "n": len(scenarios), "jobs": jobs}
+
+    def batch_prepare(self, scenarios, fs_hz):
+        """scenarios: per vector a list of (start, period, count, src_slot, freq_hz[, free_flag]), or the
+        tables pack_batch() made of it — every distinct (src_slot, freq_hz) is shifted once, in one launch
+        (b200vec_batch_prepare)."""
+        packed = scenarios if isinstance(scenarios, dict) else self.pack_batch(scenarios)
+        check(self.lib.b200vec_batch_prepare(self._ctx, packed["pk"], packed["first"], packed["n"], float(fs_hz),
+                                             self._stream()))
         self.launches += 1
-        self._batch_n = len(scenarios)
-        self._last_batch = scenarios
-        self._last_batch_jobs = len({(int(r[3]), float(r[4])) for sc in scenarios for r in sc})
+        self._batch_n = packed["n"]
+        self._last_batch = packed
+        self._last_batch_jobs = packed["jobs"]
 
     def batch_build(self, total, normalize=True, out=None, maxsq=None):
         """All vectors of the prepared batch in ONE launch (b200vec_batch_build): returns

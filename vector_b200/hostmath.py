@@ -502,25 +502,48 @@ def split_ranges(ranges, world, rank):
 
 
 def free_instance_flags(rows, lengths, total, max_instances=4_000_000):
-    """Per packet: does at least one of its instances lie in [0, total) with NO other instance (of any
-    packet, itself included) over any of its samples?  Then every sample of the packet appears
-    unsummed somewhere in the vector, so max|y_p|^2 over the whole packet is attained by the vector
-    and the in-kernel max pass may skip spans lying inside exactly one instance of it
-    (b200vec_pkt_desc.reserved bit 0).  rows: (start, period, count, slot).  Conservative: all False
-    when there are more than `max_instances` instances."""
+    """Per packet: does EVERY sample of the packet appear unsummed somewhere in [0, total) — for every packet-local
+    index n, is there an instance k with no other instance (of any packet, itself included) over sample
+    start + k*period + n?  Then max|y_p|^2 over the whole packet is attained by the vector, and the max pass may
+    skip every sample lying under exactly one instance of it (b200vec_pkt_desc.reserved bit 0; the packet maximum
+    enters the reduction from the bank).  One free-standing instance is the simple case; a train whose neighbours
+    overlap by their pre-buffers (period slightly below the packet length) qualifies too: the head is unsummed in the
+    first instance, the tail in the last, the middle in any.  rows: (start, period, count, slot).
+    Conservative: all False when there are more than `max_instances` instances."""
     rows = [(int(s), int(p), int(k)) for s, p, k, _ in rows]
     n_inst = sum(k for _, _, k in rows)
     flags = [False] * len(rows)
     if n_inst == 0 or n_inst > max_instances:
         return flags
     starts = np.concatenate([s + p * np.arange(k, dtype=np.int64) for s, p, k in rows])
-    ends = starts + np.concatenate([np.full(k, int(n), np.int64) for (_, _, k), n in zip(rows, lengths)])
+    lens = np.concatenate([np.full(k, int(n), np.int64) for (_, _, k), n in zip(rows, lengths)])
     owner = np.concatenate([np.full(k, i, np.int64) for i, (_, _, k) in enumerate(rows)])
-    order = np.argsort(starts, kind="stable")
-    st, en, ow = starts[order], ends[order], owner[order]
-    prev_end = np.concatenate([[np.iinfo(np.int64).min], np.maximum.accumulate(en)[:-1]])
-    next_start = np.concatenate([np.minimum.accumulate(st[::-1])[::-1][1:], [np.iinfo(np.int64).max]])
-    free = (prev_end <= st) & (next_start >= en) & (en <= int(total))
-    for i in np.unique(ow[free]):
-        flags[int(i)] = True
+    ends = starts + lens
+    # sweep over the instance boundaries: coverage and the sum of the active instances' ids between them
+    ids = np.arange(n_inst, dtype=np.int64)
+    pos = np.concatenate([starts, ends])
+    delta = np.concatenate([np.ones(n_inst, np.int64), -np.ones(n_inst, np.int64)])
+    idd = np.concatenate([ids, -ids])
+    order = np.lexsort((delta, pos))                      # ends before starts at equal positions
+    pos, delta, idd = pos[order], delta[order], idd[order]
+    cov = np.cumsum(delta)[:-1]
+    act = np.cumsum(idd)[:-1]
+    seg_a, seg_b = pos[:-1], pos[1:]
+    single = (cov == 1) & (seg_b > seg_a) & (seg_b <= int(total))
+    inst = act[single]                                    # the one active instance of each single-covered segment
+    la = seg_a[single] - starts[inst]                     # packet-local ranges that appear unsummed
+    lb = seg_b[single] - starts[inst]
+    ow = owner[inst]
+    for i in range(len(rows)):
+        if rows[i][2] == 0:
+            continue
+        m = ow == i
+        if not m.any():
+            continue
+        a_i, b_i = la[m], lb[m]
+        o = np.argsort(a_i, kind="stable")
+        a_i, b_i = a_i[o], b_i[o]
+        reach = np.maximum.accumulate(b_i)
+        # covered [0, L): starts at 0, no gap between consecutive (sorted) ranges, reaches L
+        flags[i] = bool(a_i[0] == 0 and reach[-1] >= int(lengths[i]) and np.all(a_i[1:] <= reach[:-1]))
     return flags
