@@ -357,3 +357,39 @@ def test_detect_packet_bounds_degenerate_lengths(eng, n, fs):
     sig = (0.01 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))).astype(np.complex64)
     sig[n // 3: n // 3 + max(1, n // 4)] += 1.0
     assert tuple(int(v) for v in vb.detect_packet_bounds(sig, fs)) == O.detect_packet_bounds(sig, fs)
+
+
+# ------------------------------------------------------------------------------ planned max pass (maxspans.cuh)
+@pytest.mark.parametrize("seed", range(10))
+def test_planned_max_pass_finds_the_exact_max(eng, seed):
+    """The max pass evaluates only the spans maxspans.cuh plans (samples under two or more instances, or under a
+    packet that never appears unsummed) and takes the rest from the bank's packet maxima: the result must be the
+    exact max |v|^2 of the whole vector — through the span kernel (b200vec_build_norm), the fused step
+    (b200vec_build_stft1024_fm_norm) and the batch build, for random scenarios including trains that overlap
+    themselves (period below the packet length) and packets placed once."""
+    from vector_b200 import dist as vdist, generate
+    rng = np.random.default_rng(900 + seed)
+    kinds = ["tone", "chirp", "bpsk", "noise", "multitone"]
+    n = int(rng.integers(300_000, 700_000)) // 512 * 512
+    rows = []
+    for _ in range(int(rng.integers(1, 5))):
+        period_ms = float(rng.choice([0.3, 0.7, 0.99, 1.0, 1.0017, 1.3, 2.9, 20.0]))     # 1.0017 ms: overlap by ~1 sample
+        rows.append((kinds[int(rng.integers(0, 5))], 0, period_ms, float(rng.uniform(0, 2.0))))
+    cfgs = O._rows_to_configs(rows)
+    pk = O.packets_for(cfgs)
+    raw = O.build_vector(pk, cfgs, n, False)[0]                    # no shift: the GPU sums are bit-exact
+    v = raw.astype(np.complex128)
+    want = float(np.max(v.real ** 2 + v.imag ** 2)) if raw.size else 0.0
+    vec, _, _, maxsq = generate.build_vector_device(cfgs, n, True, packets=pk, engine=eng)
+    assert maxsq.item() == want
+    m = np.float32(np.sqrt(want))
+    if want > 0:
+        assert np.array_equal(vec.cpu().numpy(), raw / m)
+    info = generate.prepare_bank(eng, cfgs, pk, 56e6)
+    prow = generate.placement_rows(cfgs, info, n, 56e6)
+    plan = vdist.plan_slab(n, 1, 0, 1024, 512, 1, align=512)
+    fvec, _, fmax = vdist.build_stft_slab(eng, prow, plan, True, None, fs=56e6)
+    assert fmax.item() == want and torch.equal(fvec, vec)
+    bvec, _, _, bmax = generate.build_batch_device([cfgs, cfgs[:1]], n, True,
+                                                   packets={c["file"]: p for c, p in zip(cfgs, pk)}, engine=eng)
+    assert bmax[0].item() == want and torch.equal(bvec[0, :n], vec)
