@@ -37,6 +37,9 @@ def timeit(label, env):
     for k in KEYS:
         os.environ.pop(k, None)
     os.environ.update(env)
+    import time
+    torch.cuda.synchronize()
+    time.sleep(float(os.environ.get("AB_SLEEP", "1.5")))     # let the power average fall: every variant is timed as a burst
     vec.fill_(7.0); spec.fill_(7.0)
     for _ in range(3):
         run()
