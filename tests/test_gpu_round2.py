@@ -261,6 +261,37 @@ def test_normalize_spectrogram_device_matches_oracle(eng, name):
     assert np.max(np.abs(db.cpu().numpy() - db_r)) <= 1e-4 and abs(vmin - vmin_r) <= 1e-4 and abs(vmax - vmax_r) <= 1e-4
 
 
+@pytest.mark.parametrize("kind", ["tiny1", "tiny2", "tiny7", "no_zeros", "mostly_zero", "one_value", "two_values",
+                                  "wide_range", "ragged"])
+def test_normalize_spectrogram_device_edge_cases(eng, kind):
+    """b200vec_normalize_db queues the whole chain on the device (histogram, rank arithmetic and bin picks, compaction,
+    candidate select, floor, dB map): arrays of one or a few elements, no zeros at all, almost only zeros, a single
+    repeated value (every rank in one bin: more candidates than the buffer holds -> the host-driven fallback),
+    160 dB of range, a length that is not a multiple of four."""
+    rng = np.random.default_rng(31)
+    if kind.startswith("tiny"):
+        a = np.abs(rng.standard_normal((1, int(kind[4:])))).astype(np.float32)
+    elif kind == "no_zeros":
+        a = (rng.standard_normal((300, 1000)) ** 2 + 1e-6).astype(np.float32)
+    elif kind == "mostly_zero":
+        a = np.zeros((256, 4096), np.float32)
+        a[rng.integers(0, 256, 500), rng.integers(0, 4096, 500)] = rng.uniform(1e-9, 1e-3, 500).astype(np.float32)
+    elif kind == "one_value":
+        a = np.full((1024, 3000), 3.25e-7, np.float32)
+    elif kind == "two_values":
+        a = np.where(rng.uniform(size=(2048, 1500)) < 0.3, np.float32(1e-3), np.float32(2e-9)).astype(np.float32)
+    elif kind == "wide_range":
+        a = (10.0 ** rng.uniform(-16, 0, (500, 2000))).astype(np.float32)
+    else:
+        a = (rng.standard_normal((1, 100_003)) ** 2).astype(np.float32)
+    for args in ((5, 95, 25), (10.0, 95.0, 25)):
+        db_r, vmin_r, vmax_r = O.normalize_spectrogram(a, *args)
+        db, vmin, vmax = eng.normalize_spectrogram(torch.from_numpy(a).to(eng.device), *args)
+        assert db.shape == a.shape
+        assert np.max(np.abs(db.cpu().numpy() - db_r)) <= 1e-4
+        assert abs(vmin - vmin_r) <= 1e-4 and abs(vmax - vmax_r) <= 1e-4, (kind, vmin, vmin_r, vmax, vmax_r)
+
+
 # ------------------------------------------------------------------------------ preview through the compact copy
 def test_decimated_preview_equals_strided_transform(eng):
     """create_spectrogram on a heavy signal: x[::factor] gathered once (b200vec_decimate) and transformed at

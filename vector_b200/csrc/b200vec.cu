@@ -195,6 +195,7 @@ int b200vec_destroy(b200vec_ctx *ctx) {
     if (ctx->batch.tables.ptr) cudaFree(ctx->batch.tables.ptr);
     if (ctx->batch.pin) cudaFreeHost(ctx->batch.pin);
     if (ctx->sel64.ptr) cudaFree(ctx->sel64.ptr);
+    if (ctx->k5.ptr) cudaFree(ctx->k5.ptr);
     for (SpanCache *c : {&ctx->batch.spans, &ctx->max_spans}) {
         if (c->dev.ptr) cudaFree(c->dev.ptr);
         if (c->pin) cudaFreeHost(c->pin);
@@ -822,7 +823,7 @@ static int db_impl(b200vec_ctx *ctx, const float *s_dev, int64_t n, float floor_
     if (grid > cap) grid = cap;
     if (grid < 1) grid = 1;
     float *ex_dev = reinterpret_cast<float *>(ctx->hist + kBarrierOff + 4);        // B200VEC_MAX_RANKS floats of scratch
-    db_kernel<<<(unsigned)grid, kSelThreads, 0, st>>>(s_dev, n, floor_val, out_dev, ex, ex_dev);
+    db_kernel<<<(unsigned)grid, kSelThreads, 0, st>>>(s_dev, n, floor_val, out_dev, ex, ex_dev, nullptr);
     B2_CUDA(cudaGetLastError());
     if (n_values > 0) {
         B2_CUDA(cudaMemcpyAsync(ctx->pinned, ex_dev, sizeof(float) * n_values, cudaMemcpyDeviceToHost, st));
@@ -979,15 +980,16 @@ int b200vec_select_finish(b200vec_ctx *ctx, const float *data_dev, int64_t n, co
         unsigned long long *cnt = reinterpret_cast<unsigned long long *>(ctx->top_hist + kTopBins) + 1;
         B2_CUDA(cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), st));
         const unsigned grid = (unsigned)(ctx->sm_count * 4);
-        if (ts.use_abs) sel_compact_kernel<true><<<grid, kSelThreads, 0, st>>>(data_dev, n, sel, (float *)ctx->cand.ptr, pop, cnt, ctx->hist);
-        else sel_compact_kernel<false><<<grid, kSelThreads, 0, st>>>(data_dev, n, sel, (float *)ctx->cand.ptr, pop, cnt, ctx->hist);
+        if (ts.use_abs) sel_compact_kernel<true><<<grid, kSelThreads, 0, st>>>(data_dev, n, sel, (float *)ctx->cand.ptr, pop, cnt, ctx->hist, nullptr);
+        else sel_compact_kernel<false><<<grid, kSelThreads, 0, st>>>(data_dev, n, sel, (float *)ctx->cand.ptr, pop, cnt, ctx->hist, nullptr);
         B2_CUDA(cudaGetLastError());
         long long blocks = ((long long)pop / 4 + kPickThreads * kSelUnroll - 1) / (kPickThreads * kSelUnroll);
         if (blocks > ctx->sm_count) blocks = ctx->sm_count;
         if (blocks < 1) blocks = 1;
         const float *cand = (const float *)ctx->cand.ptr;
         long long pop_ll = (long long)pop;
-        void *kargs[] = {(void *)&cand, (void *)&pop_ll, (void *)&ctx->hist};
+        const K5Plan *no_plan = nullptr;
+        void *kargs[] = {(void *)&cand, (void *)&pop_ll, (void *)&ctx->hist, (void *)&no_plan};
         B2_CUDA(cudaLaunchCooperativeKernel((const void *)sel_cand_kernel, dim3((unsigned)blocks), dim3(kPickThreads),
                                             kargs, (size_t)n_sub * kBins3 * sizeof(unsigned int), st));
         B2_CUDA(cudaMemcpyAsync(ctx->pinned, ctx->hist + kStateOff, sizeof(SelState), cudaMemcpyDeviceToHost, st));
@@ -1011,6 +1013,67 @@ int b200vec_select_finish(b200vec_ctx *ctx, const float *data_dev, int64_t n, co
 int b200vec_normalize_db(b200vec_ctx *ctx, const float *s_dev, int64_t n, double low_percentile, double high_percentile,
                          float *db_out_dev, float *values_host, int64_t *n_pos_host, void *stream) {
     B2_REQUIRE(ctx && s_dev && db_out_dev && values_host && n >= 1, "bad arguments");
+    {
+        // Fast path: the whole chain is queued at once — histogram, plan (positives, numpy's rank arithmetic, bin
+        // picks: k5_plan_kernel), compaction, candidate select, floor, dB map — and ONE small record comes back.
+        DeviceGuard g(ctx->device);
+        cudaStream_t st = (cudaStream_t)stream;
+        const unsigned long long cap = (unsigned long long)(n / 8 > (1 << 20) ? n / 8 : (1 << 20));
+        if (ctx->cand.bytes < cap * sizeof(float)) {
+            B2_CUDA(cudaStreamSynchronize(st));
+            if (ensure_scratch(ctx->cand, (size_t)cap * sizeof(float))) return 1;
+        }
+        if (ensure_scratch(ctx->k5, sizeof(K5Plan) + sizeof(K5Out) + 64)) return 1;
+        K5Plan *plan = reinterpret_cast<K5Plan *>(ctx->k5.ptr);
+        K5Out *out = reinterpret_cast<K5Out *>((char *)ctx->k5.ptr + ((sizeof(K5Plan) + 15) & ~(size_t)15));
+        const size_t top_bytes = kTopBins * sizeof(unsigned int) + 2 * sizeof(unsigned long long);
+        unsigned long long *pz = reinterpret_cast<unsigned long long *>(ctx->top_hist + kTopBins);
+        unsigned long long *cnt = pz + 1;
+        ctx->top.data = nullptr; ctx->top.n = -1;                        // no begin/finish pair is open
+        B2_CUDA(cudaMemsetAsync(ctx->top_hist, 0, top_bytes, st));
+        B2_CUDA(cudaMemsetAsync(ctx->hist, 0, sizeof(unsigned int) * kHistWords, st));
+        long long grid = (n / 4 + kSelThreads - 1) / kSelThreads + 1;
+        if (grid > (long long)ctx->sm_count * 6) grid = (long long)ctx->sm_count * 6;
+        sel_top_kernel<true><<<(unsigned)grid, kSelThreads, 0, st>>>(s_dev, n, ctx->top_hist, pz);
+        k5_plan_kernel<<<1, 1024, 0, st>>>(ctx->top_hist, pz, n, low_percentile, high_percentile, cap, ctx->hist, plan);
+        SelBins none;
+        memset(&none, 0, sizeof(none));
+        sel_compact_kernel<true><<<(unsigned)(ctx->sm_count * 4), kSelThreads, 0, st>>>(s_dev, n, none, (float *)ctx->cand.ptr,
+                                                                                        cap, cnt, ctx->hist, plan);
+        B2_CUDA(cudaGetLastError());
+        const float *cand = (const float *)ctx->cand.ptr;
+        long long n_unused = 0;
+        const K5Plan *plan_c = plan;
+        void *kargs[] = {(void *)&cand, (void *)&n_unused, (void *)&ctx->hist, (void *)&plan_c};
+        B2_CUDA(cudaLaunchCooperativeKernel((const void *)sel_cand_kernel, dim3((unsigned)ctx->sm_count), dim3(kPickThreads),
+                                            kargs, (size_t)B200VEC_MAX_RANKS * kBins3 * sizeof(unsigned int), st));
+        k5_floor_kernel<<<1, 1, 0, st>>>(ctx->hist, plan, out);
+        long long dgrid = (n / 4 + kSelThreads - 1) / kSelThreads;
+        if (dgrid > (long long)ctx->sm_count * 16) dgrid = (long long)ctx->sm_count * 16;
+        if (dgrid < 1) dgrid = 1;
+        DbExtra ex;
+        memset(&ex, 0, sizeof(ex));
+        db_kernel<<<(unsigned)dgrid, kSelThreads, 0, st>>>(s_dev, n, 0.0f, db_out_dev, ex, nullptr, out);
+        B2_CUDA(cudaGetLastError());
+        B2_CUDA(cudaMemcpyAsync(ctx->pinned, out, sizeof(K5Out), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaMemcpyAsync((char *)ctx->pinned + 1024, cnt, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaMemcpyAsync((char *)ctx->pinned + 1040, &plan->pop, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        B2_CUDA(cudaStreamSynchronize(st));
+        K5Out h;
+        memcpy(&h, ctx->pinned, sizeof(h));
+        if (!h.overflow) {
+            unsigned long long got = 0, pop = 0;
+            memcpy(&got, (char *)ctx->pinned + 1024, sizeof(got));
+            memcpy(&pop, (char *)ctx->pinned + 1040, sizeof(pop));
+            B2_REQUIRE(got == pop, "candidate count differs from the histogram (array changed during the call?)");
+            values_host[0] = h.floor_v;
+            for (int i = 0; i < 6; ++i) values_host[1 + i] = h.six[i];
+            values_host[7] = h.gamma[0]; values_host[8] = h.gamma[1];
+            if (n_pos_host) *n_pos_host = (int64_t)h.n_pos;
+            return 0;
+        }
+        // a heavily repeated non-zero value: more candidates than the buffer holds -> the host-driven path below
+    }
     int64_t n_pos = 0;
     if (b200vec_select_begin(ctx, s_dev, n, 1, &n_pos, stream)) return 1;
     // numpy's float32 index arithmetic (npquant.h): dB is monotone in |S|, so the low / high percentiles, minimum

@@ -116,6 +116,7 @@ struct b200vec_ctx {
     b200vec::BatchState batch;            // prepared scenario batch
     b200vec::SpanCache max_spans;         // must-evaluate spans of the last normalised single-vector build
     b200vec::Scratch sel64;               // state + histograms of the float64 select (packet.cuh)
+    b200vec::Scratch k5;                  // K5Plan + K5Out of b200vec_normalize_db (select.cuh)
     unsigned int *top_hist = nullptr;     // [kTopBins] u32 + one u64 (+0 count) + one u64 (candidate count)
     b200vec::Scratch cand;                // candidate array of the fast select
     b200vec::TopState top;

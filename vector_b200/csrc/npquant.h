@@ -10,6 +10,12 @@
 #include <cmath>
 #include <cstdint>
 
+#ifdef __CUDACC__
+#define B2_NPQ_HD __host__ __device__ inline
+#else
+#define B2_NPQ_HD inline
+#endif
+
 namespace b200vec {
 
 struct PctRanks {
@@ -17,11 +23,11 @@ struct PctRanks {
     float gamma;         // interpolation weight, float32
 };
 
-inline PctRanks pct_ranks_f32(int64_t count, double q) {
+B2_NPQ_HD PctRanks pct_ranks_f32(int64_t count, double q) {
     const float qq = (float)q / 100.0f;                       // np.true_divide(q, float32(100)): float32
     const float cm1 = (float)(count - 1);                     // python int -> float32 (weak scalar)
     const float vi = cm1 * qq;                                // virtual index, float32
-    float prev = std::floor(vi);
+    float prev = floorf(vi);
     float next = prev + 1.0f;                                 // may round back to prev above 2^24
     if (vi >= cm1) { prev = -1.0f; next = -1.0f; }            // _get_indexes: clamp to the last element
     if (vi < 0.0f) { prev = 0.0f; next = 0.0f; }
@@ -35,12 +41,21 @@ inline PctRanks pct_ranks_f32(int64_t count, double q) {
     return r;
 }
 
-// numpy's _lerp in float32: a + (b - a) * t, switched to b - (b - a) * (1 - t) for t >= 0.5
-inline float lerp_f32(float a, float b, float t) {
+// numpy's _lerp in float32: a + (b - a) * t, switched to b - (b - a) * (1 - t) for t >= 0.5.  Every operation is
+// rounded on its own (numpy evaluates ufunc by ufunc): on the device the intrinsics keep nvcc from contracting
+// the multiply-add pairs into FMAs.
+B2_NPQ_HD float lerp_f32(float a, float b, float t) {
+#ifdef __CUDA_ARCH__
+    const float d = __fsub_rn(b, a);
+    float out = __fadd_rn(a, __fmul_rn(d, t));
+    if (t >= 0.5f) out = __fsub_rn(b, __fmul_rn(d, __fsub_rn(1.0f, t)));
+    return out;
+#else
     const float d = b - a;
     float out = a + d * t;
     if (t >= 0.5f) out = b - d * (1.0f - t);
     return out;
+#endif
 }
 
 }  // namespace b200vec

@@ -29,6 +29,30 @@ struct SelState {
     int n_ranks;
 };
 
+// bins picked for compaction (b200vec_select_finish / k5_plan_kernel)
+struct SelBins {
+    unsigned int bin[B200VEC_MAX_RANKS];
+    int slot[B200VEC_MAX_RANKS];   // level-2 histogram (hist2[slot]) this bin's elements are counted in
+    int n;
+};
+
+struct K5Plan {
+    SelBins sel;                          // bins to compact (ascending), their level-2 histogram slots
+    unsigned long long pop;               // candidates the compaction will produce
+    unsigned long long n_pos;             // elements > 0
+    float gamma[3];                       // interpolation weights: low percentile, high percentile, floor percentile
+    int n_ranks;                          // 6, or 8 when there are positive elements
+    int sub_of[B200VEC_MAX_RANKS];        // rank r -> index in the candidate select's state, -1: the value is +0
+    int overflow;                         // 1: more candidates than the buffer holds (the caller falls back)
+};
+struct K5Out {
+    float floor_v;
+    float six[6];                         // |S| values at the six dB ranks on entry of the dB map, their dB on exit
+    float gamma[3];
+    unsigned long long n_pos;
+    int overflow;
+};
+
 __device__ __forceinline__ unsigned int f2key(float x) {
     const unsigned int u = __float_as_uint(x);
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
@@ -63,8 +87,14 @@ struct DbExtra {
 // dB are the order statistics of the dB image
 __global__ void __launch_bounds__(kSelThreads)
 db_kernel(const float *__restrict__ s, long long n, float floor_val, float *__restrict__ out,
-          const DbExtra ex, float *__restrict__ ex_out) {
-    if (blockIdx.x == 0 && (int)threadIdx.x < ex.n) ex_out[threadIdx.x] = 10.0f * log10f(fabsf(ex.v[threadIdx.x]) + floor_val);
+          const DbExtra ex, float *__restrict__ ex_out, K5Out *__restrict__ k5) {
+    if (k5) {                                     // floor and the six values were formed on the device (k5_floor_kernel)
+        if (k5->overflow) return;
+        floor_val = k5->floor_v;
+        if (blockIdx.x == 0 && threadIdx.x < 6) k5->six[threadIdx.x] = 10.0f * log10f(fabsf(k5->six[threadIdx.x]) + floor_val);
+    } else if (blockIdx.x == 0 && (int)threadIdx.x < ex.n) {
+        ex_out[threadIdx.x] = 10.0f * log10f(fabsf(ex.v[threadIdx.x]) + floor_val);
+    }
     const long long stride = (long long)gridDim.x * blockDim.x;
     const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if ((((unsigned long long)s | (unsigned long long)out) & 15ull) == 0) {       // 16-byte path, streaming loads and stores
@@ -414,12 +444,6 @@ sel_top_kernel(const float *__restrict__ x, long long n, unsigned int *__restric
         if (h[i]) atomicAdd(&hist[i], h[i]);
 }
 
-struct SelBins {
-    unsigned int bin[B200VEC_MAX_RANKS];
-    int slot[B200VEC_MAX_RANKS];   // level-2 histogram (hist2[slot]) this bin's elements are counted in
-    int n;
-};
-
 // cand[...] <- every element (after the optional abs) whose top bits name one of `sel`'s bins, +0 excluded.
 // A byte table over the 13-bit bins answers "selected?" with one shared load per element; groups of four +0
 // are skipped with one OR.  Candidates collect in a per-warp shared-memory buffer (positions from ballots, no
@@ -433,9 +457,13 @@ constexpr int kCompactFlush = kCompactBuf - 128;      // flush when a further gr
 // level 2 (sel_cand_kernel): one read of the candidate array instead of three.
 template <bool ABS>
 __global__ void __launch_bounds__(kSelThreads)
-sel_compact_kernel(const float *__restrict__ x, long long n, const SelBins sel,
+sel_compact_kernel(const float *__restrict__ x, long long n, const SelBins sel_arg,
                    float *__restrict__ cand, unsigned long long cap, unsigned long long *__restrict__ count,
-                   unsigned int *__restrict__ hist) {
+                   unsigned int *__restrict__ hist, const K5Plan *__restrict__ plan) {
+    // plan != NULL: the bins were picked on the device (k5_plan_kernel)
+    if (plan && plan->overflow) return;
+    __shared__ SelBins sel;
+    if (threadIdx.x == 0) sel = plan ? plan->sel : sel_arg;
     __shared__ unsigned char lut[kTopBins];
     __shared__ float wbuf[kSelThreads / 32][kCompactBuf];
     __shared__ unsigned int h2[B200VEC_MAX_RANKS][512];
@@ -520,7 +548,11 @@ sel_compact_kernel(const float *__restrict__ x, long long n, const SelBins sel,
 // The exact select on a candidate array whose level-2 histogram the compaction pass has already built and
 // whose state holds the 11-bit prefixes and the ranks within them: pick, one read for the last 10 bits, pick.
 __global__ void __launch_bounds__(kPickThreads, 1)
-sel_cand_kernel(const float *__restrict__ x, long long n, unsigned int *__restrict__ hist) {
+sel_cand_kernel(const float *__restrict__ x, long long n, unsigned int *__restrict__ hist, const K5Plan *__restrict__ plan) {
+    if (plan) {                                   // candidate count known on the device only
+        if (plan->overflow) return;
+        n = (long long)plan->pop;
+    }
     extern __shared__ unsigned int hs[];          // [n_ranks * kBins3]
     __shared__ unsigned char lut[2048];
     __shared__ unsigned int spref[B200VEC_MAX_RANKS];
@@ -532,6 +564,123 @@ sel_cand_kernel(const float *__restrict__ x, long long n, unsigned int *__restri
     sel_histN_body<3>(x, n, 0, hist, hs, lut, spref);
     sel_grid_sync(ctr, phase);
     if (blockIdx.x == 0) sel_pick_body<3>(hist, sh);
+}
+
+// ---------------------------------------------------------------------------------------
+// normalize_spectrogram without host round trips (b200vec_normalize_db): what the host did between the passes —
+// count the positives, numpy's rank arithmetic (npquant.h), pick every rank's 13-bit bin, set up the candidate
+// select, form the floor — runs in two tiny kernels, so the whole chain (histogram, plan, compaction, candidate
+// select, floor, dB map) is queued at once and the host reads one small record at the end.
+// one block: hist = the 13-bit histogram of |S| (+0 excluded), *n_poszero its +0 count
+__global__ void __launch_bounds__(1024)
+k5_plan_kernel(const unsigned int *__restrict__ hist13, const unsigned long long *__restrict__ n_poszero, long long n,
+               double low_q, double high_q, unsigned long long cap, unsigned int *__restrict__ hist, K5Plan *__restrict__ plan) {
+    __shared__ unsigned long long cum[kTopBins - kTopZeroBin + 1];       // exclusive prefix sums over the non-negative bins
+    __shared__ unsigned long long wsum[32];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    constexpr int NB = kTopBins - kTopZeroBin;                            // 4096
+    constexpr int PER = NB / 1024;                                        // 4
+    unsigned int c[PER];
+    unsigned long long s = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) { c[k] = hist13[kTopZeroBin + t * PER + k]; s += c[k]; }
+    unsigned long long inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long up = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += up;
+    }
+    if (lane == 31) wsum[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        unsigned long long x = wsum[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long up = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += up;
+        }
+        wsum[lane] = x;
+    }
+    __syncthreads();
+    unsigned long long run = inc - s + (w ? wsum[w - 1] : 0ull);
+#pragma unroll
+    for (int k = 0; k < PER; ++k) { cum[t * PER + k] = run; run += c[k]; }
+    if (t == 1023) cum[NB] = run;
+    __syncthreads();
+    if (t != 0) return;
+    const unsigned long long n_pos = cum[NB], n_zero = *n_poszero;
+    const PctRanks r1 = pct_ranks_f32(n, low_q), r2 = pct_ranks_f32(n, high_q);
+    PctRanks r0 = {0, 0, 0.0f};
+    long long ranks[B200VEC_MAX_RANKS] = {r1.lo, r1.hi, r2.lo, r2.hi, 0, n - 1, 0, 0};
+    int nr = 6;
+    if (n_pos > 0) {
+        r0 = pct_ranks_f32((long long)n_pos, 5.0);
+        ranks[6] = n - (long long)n_pos + r0.lo; ranks[7] = n - (long long)n_pos + r0.hi;   // the positives are the top n_pos of |S|
+        nr = 8;
+    }
+    K5Plan p;
+    p.n_pos = n_pos; p.n_ranks = nr; p.gamma[0] = r1.gamma; p.gamma[1] = r2.gamma; p.gamma[2] = r0.gamma;
+    p.sel.n = 0; p.overflow = 0;
+    int bin_of[B200VEC_MAX_RANKS];
+    unsigned long long resid[B200VEC_MAX_RANKS];
+    for (int r = 0; r < nr; ++r) {
+        unsigned long long want = (unsigned long long)ranks[r];
+        bin_of[r] = -1; resid[r] = 0;
+        if (want < n_zero) continue;                                     // inside the +0 block
+        want -= n_zero;
+        int lo = 0, hi = NB;                                             // last b with cum[b] <= want
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (cum[mid] <= want) lo = mid; else hi = mid; }
+        bin_of[r] = (int)kTopZeroBin + lo; resid[r] = want - cum[lo];
+        bool seen = false;
+        for (int q = 0; q < p.sel.n; ++q) seen = seen || p.sel.bin[q] == (unsigned)bin_of[r];
+        if (!seen) p.sel.bin[p.sel.n++] = (unsigned)bin_of[r];
+    }
+    for (int i = 1; i < p.sel.n; ++i)                                    // ascending bins = ascending values
+        for (int j = i; j > 0 && p.sel.bin[j - 1] > p.sel.bin[j]; --j) { const unsigned x = p.sel.bin[j]; p.sel.bin[j] = p.sel.bin[j - 1]; p.sel.bin[j - 1] = x; }
+    p.pop = 0;
+    auto cnt_of = [&](unsigned int bin) { return cum[bin - kTopZeroBin + 1] - cum[bin - kTopZeroBin]; };   // bin counts out of shared memory
+    for (int i = 0; i < p.sel.n; ++i) p.pop += cnt_of(p.sel.bin[i]);
+    if (p.pop > cap) p.overflow = 1;
+    // the candidate select starts at level 2 (sel_compact_kernel builds those histograms): 11-bit prefix + rank within it
+    SelState sloc;                                                      // built locally, written once
+    SelState *st = &sloc;
+    for (int r = 0; r < B200VEC_MAX_RANKS; ++r) { sloc.prefix[r] = 0u; sloc.resid[r] = 0ull; sloc.result[r] = 0u; }
+    int n_sub = 0;
+    for (int r = 0; r < nr; ++r) {
+        p.sub_of[r] = -1;
+        if (bin_of[r] < 0) continue;
+        const unsigned int p11 = (unsigned)bin_of[r] >> 2;
+        unsigned long long want = resid[r];
+        for (int i = 0; i < p.sel.n; ++i)
+            if ((p.sel.bin[i] >> 2) == p11 && p.sel.bin[i] < (unsigned)bin_of[r]) want += cnt_of(p.sel.bin[i]);
+        st->prefix[n_sub] = p11; st->resid[n_sub] = want; st->result[n_sub] = 0u;
+        p.sub_of[r] = n_sub++;
+    }
+    for (int r = nr; r < B200VEC_MAX_RANKS; ++r) p.sub_of[r] = -1;
+    st->n_ranks = n_sub; st->count = p.pop;
+    for (int i = 0; i < p.sel.n; ++i) {
+        p.sel.slot[i] = 0;
+        for (int q = 0; q < n_sub; ++q)
+            if (st->prefix[q] == (p.sel.bin[i] >> 2)) { p.sel.slot[i] = q; break; }
+    }
+    *reinterpret_cast<SelState *>(hist + kStateOff) = sloc;
+    *plan = p;
+}
+
+// one thread: the selected keys -> |S| values, the floor (utils.py:365-366) -> out (the dB map converts out->six)
+__global__ void k5_floor_kernel(const unsigned int *__restrict__ hist, const K5Plan *__restrict__ plan, K5Out *__restrict__ out) {
+    const SelState *st = reinterpret_cast<const SelState *>(hist + kStateOff);
+    float v[B200VEC_MAX_RANKS];
+    for (int r = 0; r < B200VEC_MAX_RANKS; ++r) {
+        const int i = plan->sub_of[r];
+        v[r] = i < 0 ? 0.0f : key2f(st->result[i]);
+    }
+    float floor_v = plan->n_pos > 0 ? lerp_f32(v[6], v[7], plan->gamma[2]) : 1e-12f;
+    if (1e-12f > floor_v) floor_v = 1e-12f;                              // max(floor, 1e-12)
+    out->floor_v = floor_v;
+    for (int i = 0; i < 6; ++i) out->six[i] = v[i];
+    for (int i = 0; i < 3; ++i) out->gamma[i] = plan->gamma[i];
+    out->n_pos = plan->n_pos; out->overflow = plan->overflow;
 }
 
 // out[i] = in[i * stride]: the naive decimation of create_spectrogram (utils.py:192-195, sig[::factor])
