@@ -292,6 +292,28 @@ def test_normalize_spectrogram_device_edge_cases(eng, kind):
         assert abs(vmin - vmin_r) <= 1e-4 and abs(vmax - vmax_r) <= 1e-4, (kind, vmin, vmin_r, vmax, vmax_r)
 
 
+@pytest.mark.parametrize("off", [1, 2, 3])
+def test_order_statistics_on_misaligned_arrays(eng, off):
+    """The histogram / compaction passes read 16-byte groups from the first aligned element on and sweep the ragged
+    ends separately: a view that starts 4, 8 or 12 bytes past a 16-byte boundary must give the same exact answers."""
+    rng = np.random.default_rng(40 + off)
+    n = 300_007
+    a = (rng.standard_normal(n + off) ** 2).astype(np.float32)
+    a[rng.integers(0, n, n // 3)] = 0.0
+    base = torch.from_numpy(a).to(eng.device)
+    d = base[off:]
+    assert d.data_ptr() % 16 == 4 * off
+    srt = np.sort(a[off:])
+    n_pos = eng.select_begin(d, use_abs=True)
+    assert n_pos == int((a[off:] > 0).sum())
+    ranks = [0, n // 20, n // 2, n - 2, n - 1]
+    assert np.array_equal(eng.select_finish(d, ranks), srt[ranks])
+    assert np.array_equal(eng.select_ranks(d, ranks), srt[ranks])
+    db_r, vmin_r, vmax_r = O.normalize_spectrogram(a[off:].reshape(1, -1), 5, 95, 25)
+    db, vmin, vmax = eng.normalize_spectrogram(d.view(1, -1), 5, 95, 25)
+    assert np.max(np.abs(db.cpu().numpy() - db_r)) <= 1e-4 and abs(vmin - vmin_r) <= 1e-4 and abs(vmax - vmax_r) <= 1e-4
+
+
 # ------------------------------------------------------------------------------ preview through the compact copy
 def test_decimated_preview_equals_strided_transform(eng):
     """create_spectrogram on a heavy signal: x[::factor] gathered once (b200vec_decimate) and transformed at
