@@ -44,6 +44,7 @@ struct SpanArgs {
     const MaxSpan *spans;        // MAXONLY / NORM: the spans evaluated (maxspans.cuh), sorted by vector
     long long n_spans;
     unsigned int *ctr;           // [0] next work item, [2] grid barrier; zeroed on the stream before every launch
+    int chunk;                   // halves per work item (set by launch_span)
 };
 
 template <bool BATCH>
@@ -210,7 +211,7 @@ span_kernel(const __grid_constant__ SpanArgs a) {
     // -------------------------------------------------------------------- pass B: place, scale, store
     const long long n = a.hi - a.lo;
     const long long halves = (n + 511) / 512;
-    constexpr int kChunk = BATCH ? kSpChunkBatch : kSpChunk;
+    const int kChunk = a.chunk;
     const long long ipv = (halves + kChunk - 1) / kChunk;                     // items per vector
     const long long n_items = ipv * a.n_vec;
     const bool scaled = a.mode == B200VEC_BUILD_SCALE || a.mode == kSpNorm;
@@ -279,7 +280,12 @@ inline int launch_span(b200vec_ctx *ctx, SpanArgs &a, cudaStream_t st) {
         B2_REQUIRE(occ[batch] > 0, "span_kernel does not fit an SM");
     }
     const long long halves = n > 0 ? (n + 511) / 512 : 0;
-    const int chunk = batch ? kSpChunkBatch : kSpChunk;
+    // batch: 16-half items amortise the per-item descriptor fetch, as long as every warp still gets >= ~24 of them
+    // (32 vectors per GPU at cfg5 / 8 GPUs would leave 6 per warp: a 13 % tail); halve the item until it does
+    const long long cap_warps = (long long)ctx->sm_count * occ[batch] * kSpWarps;
+    int chunk = batch ? kSpChunkBatch : kSpChunk;
+    while (batch && chunk > kSpChunk && (halves + chunk - 1) / chunk * a.n_vec < 24 * cap_warps) chunk >>= 1;
+    a.chunk = chunk;
     const long long items = pass_b ? (halves + chunk - 1) / chunk * a.n_vec : 0;
     const long long units = a.n_spans;
     const long long work = items > units ? items : units;
