@@ -202,34 +202,37 @@ B2_HD void fft32_windowed_q(cf32 (&v)[32], const W4 &w4) {
     dit_tail(v);
 }
 
-// ---- second transform: v[i] holds RAW B_l[q] with l = brev5(i); tw(l) returns W1024^(l q).
-// On exit v[s] = X[q + 32 s].
-template <int P, class TW>
-B2_HD void tw_bfly(cf32 (&v)[32], const TW &tw) {
+// ---- second transform: v[i] holds RAW B_l[q] with l = brev5(i).  On exit v[s] = X[q + 32 s].
+// The W1024^(l q) twiddles are folded into the first stage: butterfly P pairs l_a = brev5(2 P) with
+// l_b = l_a + 16, so  u = T_a a,  y0 = u + T_b b,  y1 = 2 u - y0  with T_b = T_a * W1024^(16 q).
+// Only HALF the twiddles are read: the table holds W1024^(q l_a) (one 8-byte load per butterfly) and
+// c16 = W1024^(16 q) is a per-lane constant; T_b costs two more packed instructions instead of a second load —
+// the shared-memory pipe, not the FMA pipe, is this kernel's co-bottleneck (profiles/README.md).
+template <int P, class TW1>
+B2_HD void tw1_bfly(cf32 (&v)[32], const TW1 &tw1, const cf32 c16) {
     constexpr int i = 2 * P;
-    constexpr int la = brev5(i), lb = brev5(i + 1);
-    cf32 u;
-    if constexpr (la == 0) {
-        u = v[i];
+    cf32 u, tb;
+    if constexpr (P == 0) {                     // la = 0: twiddles 1 and c16
+        u = v[i]; tb = c16;
     } else {
-        const cf32 ta = tw(la);
+        const cf32 ta = tw1(P);
+        tb = c_twmul(ta, c16);
         u = c_twmul(v[i], ta);
     }
-    const cf32 tb = tw(lb);
     const cf32 y0 = c_twmul_add(v[i + 1], tb, u);
     v[i + 1] = c_2a_minus(u, y0);
     v[i] = y0;
 }
-template <class TW>
-B2_HD void fft32_twiddled(cf32 (&v)[32], const TW &tw) {
-    tw_bfly<0>(v, tw); tw_bfly<1>(v, tw); tw_bfly<2>(v, tw); tw_bfly<3>(v, tw);
-    tw_bfly<4>(v, tw); tw_bfly<5>(v, tw); tw_bfly<6>(v, tw); tw_bfly<7>(v, tw);
-    tw_bfly<8>(v, tw); tw_bfly<9>(v, tw); tw_bfly<10>(v, tw); tw_bfly<11>(v, tw);
-    tw_bfly<12>(v, tw); tw_bfly<13>(v, tw); tw_bfly<14>(v, tw); tw_bfly<15>(v, tw);
+template <class TW1>
+B2_HD void fft32_twiddled_half(cf32 (&v)[32], const TW1 &tw1, const cf32 c16) {
+    tw1_bfly<0>(v, tw1, c16); tw1_bfly<1>(v, tw1, c16); tw1_bfly<2>(v, tw1, c16); tw1_bfly<3>(v, tw1, c16);
+    tw1_bfly<4>(v, tw1, c16); tw1_bfly<5>(v, tw1, c16); tw1_bfly<6>(v, tw1, c16); tw1_bfly<7>(v, tw1, c16);
+    tw1_bfly<8>(v, tw1, c16); tw1_bfly<9>(v, tw1, c16); tw1_bfly<10>(v, tw1, c16); tw1_bfly<11>(v, tw1, c16);
+    tw1_bfly<12>(v, tw1, c16); tw1_bfly<13>(v, tw1, c16); tw1_bfly<14>(v, tw1, c16); tw1_bfly<15>(v, tw1, c16);
     dit_tail(v);
 }
 
-// Same transform with the twiddles fetched two at a time: tq[P] = (W1024^(q la), W1024^(q lb)) with
+// (A/B builds only, pipe1024.cuh) Same transform with the twiddles fetched two at a time: tq[P] = (W1024^(q la), W1024^(q lb)) with
 // la = brev5(2 P), lb = brev5(2 P + 1) — the order the first stage consumes them, one 16-byte
 // load per butterfly (table built by get_tw1024_pairs).
 struct cf32x2 {
@@ -256,6 +259,14 @@ B2_HD void fft32_twiddled_pairs(cf32 (&v)[32], const TW2 &tw2) {
     tw2_bfly<8>(v, tw2); tw2_bfly<9>(v, tw2); tw2_bfly<10>(v, tw2); tw2_bfly<11>(v, tw2);
     tw2_bfly<12>(v, tw2); tw2_bfly<13>(v, tw2); tw2_bfly<14>(v, tw2); tw2_bfly<15>(v, tw2);
     dit_tail(v);
+}
+
+
+// tw(l) returns W1024^(l q): the form the tile kernel and the host harness use (same arithmetic, bit for bit)
+template <class TW>
+B2_HD void fft32_twiddled(cf32 (&v)[32], const TW &tw) {
+    const cf32 c16 = tw(16);
+    fft32_twiddled_half(v, [&tw](int P) { return tw(brev5(2 * P)); }, c16);
 }
 
 }  // namespace b200vec

@@ -250,11 +250,12 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         wf_fence_async();
     }
 
-    // twiddle pairs in the order the first stage of T2 consumes them: tw4[P][q] = (W^(q la), W^(q lb)),
-    // la = brev5(2 P), lb = brev5(2 P + 1): one 16-byte load per butterfly
+    // twiddles in the order the first stage of T2 consumes them: tw[P][q] = W^(q la), la = brev5(2 P) — W^(q lb),
+    // lb = la + 16, is formed from it in registers: one 8-byte load per butterfly
     for (int i = tid; i < 1024; i += kWfThreads) {
         const int q = i & 31, k = i >> 5;                    // k = 2 P + c
-        tw[(k >> 1) * 64 + q * 2 + (k & 1)] = __ldg(a.tw + brev5(k) * 32 + q);
+        // half table (fft32.cuh): slot P holds W^(q la(P)), la = brev5(2 P); slot 0 (la = 0) holds c16 = W^(16 q) instead
+        if ((k & 1) == 0) tw[(k >> 1) * 32 + q] = __ldg(a.tw + (k == 0 ? 16 : brev5(k)) * 32 + q);
     }
     {
         const float rs = sqrtf(a.scale);                    // |X|^2 * scale = |FFT(x * w * sqrt(scale))|^2
@@ -378,7 +379,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
 
     const long long n_vec = a.place.hi - a.place.lo;
     const float4 *wl = win4 + lane;
-    const float4 *tq4 = reinterpret_cast<const float4 *>(tw) + lane;
+    const float2 *tq2 = tw + lane;                           // half twiddle table, slot 0 = W^(16 q)
     float2 *ex_w = exch + lane * kWfExPitch;                 // T1 writes row l = lane
     const float2 *ex_r = exch + lane;                        // T2 reads column q = lane
     unsigned anybits = 0;
@@ -499,7 +500,10 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
                         v[brev5(l)].x = s.x; v[brev5(l)].y = s.y;
                     }
                     __syncwarp();                            // the block may be overwritten by the next frame
-                    if (!(DBG & 4)) fft32_twiddled_pairs(v, [tq4](int P) { const float4 w = tq4[32 * P]; return cf32x2{w.x, w.y, w.z, w.w}; });
+                    if (!(DBG & 4)) {
+                        const float2 c = tq2[0];
+                        fft32_twiddled_half(v, [tq2](int P) { const float2 w = tq2[32 * P]; return cf32{w.x, w.y}; }, cf32{c.x, c.y});
+                    }
                     // BULK: the frame's 4 KB are staged in the (now free) exchange block and leave as one bulk copy
                     float *o = BULK ? reinterpret_cast<float *>(exch) + lane : of + lane;
 #pragma unroll
