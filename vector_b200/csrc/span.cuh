@@ -129,7 +129,9 @@ __device__ __forceinline__ bool sp_build_half(const SpanArgs &a, const PlaceDesc
 
 // (Measured: capping registers for 4 or 5 CTAs per SM instead of 3, or two staging blocks per warp, does not help —
 // 102 -> 111 / 118 us at cfg2 store-only — although the warps mostly wait on the L2 gather.)
-template <bool BATCH>
+// CHUNK = halves per work item, a compile-time constant: with a run-time item size the single-vector store pass
+// ran at 96 us instead of 86 us (cfg2).
+template <bool BATCH, int CHUNK = kSpChunk>
 __global__ void __launch_bounds__(kSpThreads)
 span_kernel(const __grid_constant__ SpanArgs a) {
     extern __shared__ __align__(16) unsigned char sp_smem[];
@@ -211,7 +213,7 @@ span_kernel(const __grid_constant__ SpanArgs a) {
     // -------------------------------------------------------------------- pass B: place, scale, store
     const long long n = a.hi - a.lo;
     const long long halves = (n + 511) / 512;
-    const int kChunk = a.chunk;
+    constexpr int kChunk = CHUNK;
     const long long ipv = (halves + kChunk - 1) / kChunk;                     // items per vector
     const long long n_items = ipv * a.n_vec;
     const bool scaled = a.mode == B200VEC_BUILD_SCALE || a.mode == kSpNorm;
@@ -251,11 +253,15 @@ span_kernel(const __grid_constant__ SpanArgs a) {
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+template <bool BATCH, int CHUNK>
+inline cudaError_t span_attr() {
+    cudaError_t e = cudaFuncSetAttribute(span_kernel<BATCH, CHUNK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmem);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(span_kernel<BATCH, CHUNK>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+}
 inline int span_setup() {
-    B2_CUDA(cudaFuncSetAttribute(span_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmem));
-    B2_CUDA(cudaFuncSetAttribute(span_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpSmem));
-    B2_CUDA(cudaFuncSetAttribute(span_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
-    B2_CUDA(cudaFuncSetAttribute(span_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+    B2_CUDA((span_attr<false, kSpChunk>()));
+    B2_CUDA((span_attr<true, 16>())); B2_CUDA((span_attr<true, 8>())); B2_CUDA((span_attr<true, 4>()));
     return 0;
 }
 
@@ -275,8 +281,8 @@ inline int launch_span(b200vec_ctx *ctx, SpanArgs &a, cudaStream_t st) {
     a.ctr = ctx->sp_ctr;
     static int occ[2] = {0, 0};            // resident CTAs per SM (register / shared-memory limited)
     if (!occ[batch]) {
-        if (batch) B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1], span_kernel<true>, kSpThreads, kSpSmem));
-        else B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0], span_kernel<false>, kSpThreads, kSpSmem));
+        if (batch) B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1], span_kernel<true, 16>, kSpThreads, kSpSmem));
+        else B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0], span_kernel<false, kSpChunk>, kSpThreads, kSpSmem));
         B2_REQUIRE(occ[batch] > 0, "span_kernel does not fit an SM");
     }
     const long long halves = n > 0 ? (n + 511) / 512 : 0;
@@ -295,14 +301,13 @@ inline int launch_span(b200vec_ctx *ctx, SpanArgs &a, cudaStream_t st) {
     if (grid < 1) grid = 1;
     B2_REQUIRE(items < 0x7fffffffLL - cap * kSpWarps, "too many work items for one launch (split the batch)");
     void *kargs[] = {&a};
-    if (a.mode == kSpNorm) {               // grid barrier between the passes: cooperative launch
-        if (batch) B2_CUDA(cudaLaunchCooperativeKernel((const void *)span_kernel<true>, dim3((unsigned)grid), dim3(kSpThreads), kargs, kSpSmem, st));
-        else B2_CUDA(cudaLaunchCooperativeKernel((const void *)span_kernel<false>, dim3((unsigned)grid), dim3(kSpThreads), kargs, kSpSmem, st));
-    } else if (batch) {
-        span_kernel<true><<<(unsigned)grid, kSpThreads, kSpSmem, st>>>(a);
-    } else {
-        span_kernel<false><<<(unsigned)grid, kSpThreads, kSpSmem, st>>>(a);
-    }
+    const void *fn = !batch ? (const void *)span_kernel<false, kSpChunk>
+                   : chunk == 16 ? (const void *)span_kernel<true, 16>
+                   : chunk == 8 ? (const void *)span_kernel<true, 8> : (const void *)span_kernel<true, 4>;
+    if (a.mode == kSpNorm)                 // grid barrier between the passes: cooperative launch
+        B2_CUDA(cudaLaunchCooperativeKernel(fn, dim3((unsigned)grid), dim3(kSpThreads), kargs, kSpSmem, st));
+    else
+        B2_CUDA(cudaLaunchKernel(fn, dim3((unsigned)grid), dim3(kSpThreads), kargs, kSpSmem, st));
     B2_CUDA(cudaGetLastError());
     return 0;
 }
