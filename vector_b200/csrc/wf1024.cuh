@@ -252,19 +252,22 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
 
     // twiddles in the order the first stage of T2 consumes them: tw[P][q] = W^(q la), la = brev5(2 P) — W^(q lb),
     // lb = la + 16, is formed from it in registers: one 8-byte load per butterfly
-    for (int i = tid; i < 1024; i += kWfThreads) {
-        const int q = i & 31, k = i >> 5;                    // k = 2 P + c
-        // half table (fft32.cuh): slot P holds W^(q la(P)), la = brev5(2 P); slot 0 (la = 0) holds c16 = W^(16 q) instead
-        if ((k & 1) == 0) tw[(k >> 1) * 32 + q] = __ldg(a.tw + (k == 0 ? 16 : brev5(k)) * 32 + q);
-    }
-    {
+    auto build_tables = [&]() {
+        for (int i = tid; i < 1024; i += kWfThreads) {
+            const int q = i & 31, k = i >> 5;                // k = 2 P + c
+            // half table (fft32.cuh): slot P holds W^(q la(P)), la = brev5(2 P); slot 0 (la = 0) holds c16 = W^(16 q) instead
+            if ((k & 1) == 0) tw[(k >> 1) * 32 + q] = __ldg(a.tw + (k == 0 ? 16 : brev5(k)) * 32 + q);
+        }
         const float rs = sqrtf(a.scale);                    // |X|^2 * scale = |FFT(x * w * sqrt(scale))|^2
         float *wf = reinterpret_cast<float *>(win4);
         for (int i = tid; i < 1024; i += kWfThreads) {      // i = (k * 32 + lane) * 4 + c  ->  tap j = brev5(4 k + c) of lane
             const int c = i & 3, ln = (i >> 2) & 31, k = i >> 7;
             wf[i] = __ldg(a.window + ln + 32 * brev5(4 * k + c)) * rs;
         }
-    }
+    };
+    // with an in-kernel max pass the tables are built while the grid barrier fills (nothing before it needs them)
+    const bool norm_pass = !PLAIN && (a.mode == kWfAutoNorm || a.mode == kWfAutoNormPeer);
+    if (!norm_pass) build_tables();
     const unsigned long long keep = wf_policy_evict_last();
     float scl = 1.0f;
     if (a.mode == B200VEC_BUILD_SCALE) {
@@ -272,7 +275,7 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);        // numpy's complex64 / float32: multiply by the fp32 reciprocal
     }
     __syncthreads();
-    if (!PLAIN && (a.mode == kWfAutoNorm || a.mode == kWfAutoNormPeer)) {
+    if (norm_pass) {
         // Pass A inside the kernel: every warp evaluates its share of the spans that can hold the max of the
         // whole vector (maxspans.cuh: the pieces of hostmath.max_eval_ranges under >= 2 instances; what lies
         // under one instance is covered by the packet maxima below), the grid meets at a barrier (cooperative
@@ -314,9 +317,12 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
             if (pm) atomicMax(slot, pm);
         }
         __syncthreads();
-        if (tid == 0) {                                      // grid barrier
+        if (tid == 0) {                                      // grid barrier: arrive ...
             __threadfence();
             atomicAdd(a.ctr + 2, 1u);
+        }
+        build_tables();                                      // ... build the window / twiddle tables while the others arrive ...
+        if (tid == 0) {                                      // ... wait
             while (*reinterpret_cast<volatile unsigned int *>(a.ctr + 2) < gridDim.x) __nanosleep(40);
             __threadfence();
         }
