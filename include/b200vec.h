@@ -201,6 +201,16 @@ int b200vec_build_stft1024_fm_norm(b200vec_ctx *ctx, const b200vec_pkt_desc *des
                                    int64_t frame_lo, int64_t n_frames, float *spec_out_dev, int64_t out_ld,
                                    int *nonzero_flag_dev, void *stream);
 
+/* Periodic spectrogram tiling for dense periodic vectors (BASELINE.json configs[3]): where the vector repeats bit for
+ * bit with period T, its full-rate spectrogram (hann 1024 / hop 512, vector_analyzer/spectrogram_analysis.py:35-49)
+ * repeats with period lcm(T, 512) / 512 frames — frame f holds the same 1024 samples as frame f - period.  Copies,
+ * in frame-major memory (see b200vec_build_stft1024_fm),
+ *   spec[(frame_dst0 + i) * out_ld ..] = spec[(frame_src0 + (frame_dst0 + i - frame_src0) mod period_frames) * out_ld ..]
+ * for 0 <= i < n_frames (1024 bins each); frame_dst0 >= frame_src0 + period_frames.  The caller (dist.build_stft_slab,
+ * hostmath.tile_plan) guarantees that every destination frame lies inside the bit-exactly periodic part. */
+int b200vec_replicate_frames(b200vec_ctx *ctx, float *spec_dev, int64_t out_ld, int64_t frame_src0, int64_t period_frames,
+                             int64_t frame_dst0, int64_t n_frames, void *stream);
+
 /* b200vec_stft for the full-rate analysis shape (hann-type window of 1024 taps, nperseg = nfft = 1024,
  * hop 512, stride 1; vector_analyzer/spectrogram_analysis.py:40-53, mat_analyzer.py:37-45) with the
  * spectrogram stored FRAME-MAJOR: out_dev[(f-frame_lo)*out_ld + row] (see b200vec_build_stft1024_fm).

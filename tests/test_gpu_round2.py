@@ -171,6 +171,35 @@ def test_periodic_tiling_is_bit_exact(eng, world):
         assert tp["T"] == 2_400_000 and tp["x1"] % 512 == 0 and tp["x2"] % 512 == 0 and tp["x2"] - tp["x1"] > 2_400_000
 
 
+@pytest.mark.parametrize("periods,pf", [((2048, 3072), 12), ((1000, 1500), 375), ((1536,), 3)])
+def test_spectrogram_tiling_is_bit_exact(eng, periods, pf):
+    """Where the vector repeats with period T its hop-512 spectrogram repeats every lcm(T, 512) / 512 frames: with
+    spec_tile only the first such period of the tiled part is transformed, the vector comes from the vector tile
+    through the span kernel and the remaining frames are copies (b200vec_replicate_frames).  Must equal the untiled
+    build bit for bit — T a multiple of 512 (pf = T / 512), T = 3000 (pf = 375 = lcm / 512), one packet."""
+    from vector_b200 import dist as vdist, hostmath as H
+    rng = np.random.default_rng(77)
+    n = 1_000_000 // 512 * 512 + 300
+    rows, lengths = [], []
+    for slot, per in enumerate(periods):
+        y = (rng.standard_normal(3001 + 200 * slot) + 1j * rng.standard_normal(3001 + 200 * slot)).astype(np.complex64)
+        eng.bank_upload(slot, y)
+        eng.bank_commit(slot, 0.0, 56e6)
+        start = 40 * slot
+        rows.append((start, per, H.instance_count(start, per, y.size, n), slot))
+        lengths.append(y.size)
+    tp = H.tile_plan(rows, lengths, n, 0, n, min_density=0.0, min_gain=0.25)
+    assert tp is not None and tp["spec_period_frames"] == pf
+    plan = vdist.plan_slab(n, 1, 0, 1024, 512, 1, align=512)
+    ref_vec, ref_spec, ref_m = [t.clone() for t in vdist.build_stft_slab(eng, rows, plan, True, None, tile=False)]
+    l0 = eng.launches
+    vec, spec, m = vdist.build_stft_slab(eng, rows, plan, True, None, tile=True, spec_tile=True)
+    assert eng.launches - l0 == 5                                   # head, one period, vector, frame copies, tail
+    assert torch.equal(m, ref_m) and torch.equal(vec, ref_vec) and torch.equal(spec, ref_spec)
+    vec2, spec2, _ = vdist.build_stft_slab(eng, rows, plan, True, None, tile=True, spec_tile=False)
+    assert torch.equal(vec2, ref_vec) and torch.equal(spec2, ref_spec)
+
+
 def test_attached_slot_places_like_an_uploaded_packet(eng):
     """b200vec_bank_attach: caller-owned device memory as a bank slot, no copy."""
     from vector_b200._lib import B200VecError, BUILD_STORE

@@ -79,6 +79,8 @@ _SIGNATURES = {
                                                       C.c_void_p, C.c_float, C.c_int64, C.c_int64, C.c_void_p,
                                                       C.c_int64, C.c_void_p, C.c_void_p]),
     "b200vec_db": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]),
+    "b200vec_replicate_frames": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
+                                           C.c_void_p]),
     "b200vec_normalize_db": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_double, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_void_p]),
     "b200vec_select_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),

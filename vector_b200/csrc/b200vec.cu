@@ -594,6 +594,24 @@ int b200vec_batch_build(b200vec_ctx *ctx, int64_t total, void *out_dev, int64_t 
 }
 
 // ---------------------------------------------------------------------------------------
+int b200vec_replicate_frames(b200vec_ctx *ctx, float *spec_dev, int64_t out_ld, int64_t frame_src0, int64_t period_frames,
+                             int64_t frame_dst0, int64_t n_frames, void *stream) {
+    B2_REQUIRE(ctx && spec_dev, "NULL argument");
+    B2_REQUIRE(out_ld >= 1024 && (out_ld & 3) == 0 && ((uintptr_t)spec_dev & 15) == 0,
+               "frame-major spectrogram: out_ld >= 1024, a multiple of 4, 16-byte aligned base");
+    B2_REQUIRE(frame_src0 >= 0 && period_frames >= 1 && n_frames >= 0 && frame_dst0 >= frame_src0 + period_frames,
+               "the destination frames must lie past the source period");
+    if (n_frames == 0) return 0;
+    DeviceGuard g(ctx->device);
+    long long grid = (n_frames + 7) / 8;
+    const long long cap = (long long)ctx->sm_count * 8;
+    if (grid > cap) grid = cap;
+    replicate_frames_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(spec_dev, out_ld, frame_src0, period_frames,
+                                                                               frame_dst0, n_frames);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_t in_len,
                  int64_t stride, int nperseg, int hop, int nfft, const float *window_dev,
                  float scale, int64_t frame_lo, int64_t n_frames, float *out_dev,

@@ -348,4 +348,31 @@ batch_shift_kernel(const ShiftJob *__restrict__ jobs, double fs) {
     if ((threadIdx.x & 31) == 0 && m > 0.0) atomicMax(jb.pmax, (unsigned long long)__double_as_longlong(m));
 }
 
+// ---------------------------------------------------------------------------------------
+// Periodic spectrogram tiling (dense periodic vectors, BASELINE.json configs[3]).  Where the vector repeats bit for
+// bit with period T (hostmath.tile_plan), its full-rate spectrogram repeats with period Pf = lcm(T, 512) / 512
+// frames: frame f is the same 1024 samples, hence the same 4 KB, as frame f - Pf.  The steady part of a slab's
+// spectrogram is therefore COPIED from the Pf frames before it (frame-major memory: dst[f] = src[f0 + (f - f0) mod Pf])
+// instead of transformed — the tile (38 MB at cfg4) is read through L2 with evict_last, the copies stream out.
+// One warp per frame and iteration, 16-byte accesses.
+__global__ void __launch_bounds__(256)
+replicate_frames_kernel(float *__restrict__ spec, long long ld, long long f_src0, long long period, long long f_dst0,
+                        long long n_frames) {
+    const unsigned long long keep = wf_policy_evict_last();
+    const int lane = threadIdx.x & 31;
+    const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long i = gw; i < n_frames; i += nw) {
+        const long long f = f_dst0 + i;
+        const float4 *src = reinterpret_cast<const float4 *>(spec + (f_src0 + (f - f_src0) % period) * ld) + lane;
+        float4 *dst = reinterpret_cast<float4 *>(spec + f * ld) + lane;
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+                         : "=f"(v[k].x), "=f"(v[k].y), "=f"(v[k].z), "=f"(v[k].w) : "l"(src + 32 * k), "l"(keep));
+#pragma unroll
+        for (int k = 0; k < 8; ++k) __stcs(dst + 32 * k, v[k]);
+    }
+}
+
 }  // namespace b200vec

@@ -113,12 +113,13 @@ def stft_slab(engine, vec, plan, window="hann", nperseg=1024, noverlap=512, nfft
 
 
 TILE_SLOT = 62                 # bank slot the periodic tile is attached to (the vector build uses 0..31)
+SPEC_TILE_BYTES = 64 << 20     # largest spectrogram period (frames * 4 KB) that is tiled: it has to stay in the 126 MB L2
 REDUNDANT_MAX_SAMPLES = 16_000_000
 
 
 def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6, window="hann",
                     scaling="density", out_vec=None, out_spec=None, peer=None, tile="auto",
-                    redundant_max=REDUNDANT_MAX_SAMPLES):
+                    redundant_max=REDUNDANT_MAX_SAMPLES, spec_tile=True):
     """Owned slab of the vector AND this rank's spectrogram columns (hann-1024/512 analysis STFT of
     vector_analyzer/spectrogram_analysis.py:35-49) with the fused kernel: one launch that finds the
     max, places, scales, stores the vector and transforms it out of registers.  `plan` must be cut on
@@ -135,7 +136,9 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
     Periodic tiling (tile="auto" | True | False, hostmath.tile_plan): when the packet trains overlap
     densely and share a common period T that fits the L2, the steady part of the slab repeats its first T
     samples bit for bit; it is then placed from the vector itself (one L2 read per sample instead of one
-    per overlapping instance) by a second launch that names out_vec[x1 - T, x1) as an attached bank slot."""
+    per overlapping instance) by a second launch that names out_vec[x1 - T, x1) as an attached bank slot.
+    spec_tile: the spectrogram of that part repeats every lcm(T, 512) / 512 frames; when one such period fits
+    the L2 only its first period is transformed and the rest are copies (hostmath.tile_plan)."""
     import torch
     from ._lib import BUILD_MAXONLY, BUILD_SCALE, BUILD_STORE
     nf = plan.frame_hi - plan.frame_lo
@@ -202,8 +205,19 @@ def build_stft_slab(engine, rows, plan, normalize=True, reduce_max=None, fs=56e6
         t = tp["T"]
         engine.bank_attach(TILE_SLOT, vec_at(x1 - t)[:t])
         tdescs, tnd = engine.make_descs([(x1, t, tp["count"], TILE_SLOT)])
-        engine.build_stft1024(tdescs, tnd, x1, x2, vec_at(x1), BUILD_STORE, x1 // 512, x2 // 512 - x1 // 512,
-                              spec_at(x1 // 512), window=window, fs=fs, scaling=scaling)
+        pf = tp["spec_period_frames"]
+        xs = x1 + pf * 512                                   # end of the first spectrogram period of the tiled part
+        if spec_tile and pf * 4096 <= SPEC_TILE_BYTES and xs + 512 * max(pf // 4, 1) <= x2:
+            # The spectrogram of the periodic part repeats every pf frames: transform ONE period, then the vector
+            # comes from the vector tile (span kernel, no transforms) and the frames are copies of that period
+            # (b200vec_replicate_frames) — bit for bit what transforming them would give.
+            engine.build_stft1024(tdescs, tnd, x1, xs, vec_at(x1), BUILD_STORE, x1 // 512, pf,
+                                  spec_at(x1 // 512), window=window, fs=fs, scaling=scaling)
+            engine.build_pass(tdescs, tnd, xs, x2, vec_at(xs), BUILD_STORE)
+            engine.replicate_frames(out_spec, x1 // 512 - frame_lo, pf, xs // 512 - frame_lo, x2 // 512 - xs // 512)
+        else:
+            engine.build_stft1024(tdescs, tnd, x1, x2, vec_at(x1), BUILD_STORE, x1 // 512, x2 // 512 - x1 // 512,
+                                  spec_at(x1 // 512), window=window, fs=fs, scaling=scaling)
         # ---- launch 3: the tail [x2, hi) from the packet bank again
         if x2 < plan.hi or x2 // 512 < plan.frame_hi:
             engine.build_stft1024(descs, nd, x2, plan.hi, vec_at(x2), BUILD_SCALE if normalize else BUILD_STORE,

@@ -280,6 +280,15 @@ class Engine:
         self.launches += 1
         return out
 
+    def replicate_frames(self, spec, frame_src0, period_frames, frame_dst0, n_frames):
+        """spec[:, frame_dst0 + i] = spec[:, frame_src0 + (frame_dst0 + i - frame_src0) % period_frames] for a
+        frame-major spectrogram tensor (b200vec_replicate_frames): the periodic tiling of a dense vector's map."""
+        if not (spec.dim() == 2 and spec.stride(0) == 1 and spec.stride(1) >= 1024):
+            raise ValueError("replicate_frames needs frame-major spectrogram memory")
+        check(self.lib.b200vec_replicate_frames(self._ctx, self._ptr(spec), spec.stride(1), int(frame_src0),
+                                                int(period_frames), int(frame_dst0), int(n_frames), self._stream()))
+        self.launches += 1
+
     # ------------------------------------------------------------------ dB / percentiles
     def db(self, s, floor_val, out=None):
         s = s.contiguous()

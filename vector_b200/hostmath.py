@@ -463,7 +463,8 @@ def tile_plan(rows, lengths, total, lo, hi, max_tile_samples=6_000_000, min_dens
     (one read per sample instead of one per overlapping instance).  Returns None, or
     dict(x1, x2, T, count): [lo, x1) and [x2, hi) are built from the packet bank, [x1, x2) from
     out[x1 - T, x1) placed at x1, x1 + T, ... (`count` instances, the last also covering the 512-sample
-    halo past x2); x1 and x2 are multiples of 512."""
+    halo past x2); x1 and x2 are multiples of 512.  spec_period_frames = lcm(T, 512) / 512: frame f of the
+    hop-512 spectrogram holds the same samples as frame f - spec_period_frames wherever both lie in [x1, x2)."""
     cp = common_period(rows, lengths, total)
     if cp is None:
         return None
@@ -480,7 +481,8 @@ def tile_plan(rows, lengths, total, lo, hi, max_tile_samples=6_000_000, min_dens
         x2 = hi // 512 * 512
     if x2 - x1 < max(512, int(min_gain * t)):
         return None
-    return dict(x1=x1, x2=x2, T=t, count=-(-(x2 + 512 - x1) // t))
+    # the full-rate spectrogram (hop 512) of the periodic part repeats every lcm(T, 512) / 512 frames
+    return dict(x1=x1, x2=x2, T=t, count=-(-(x2 + 512 - x1) // t), spec_period_frames=t // math.gcd(t, 512))
 
 
 def split_ranges(ranges, world, rank):
