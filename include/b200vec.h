@@ -334,6 +334,23 @@ int b200vec_median2_rows(b200vec_ctx *ctx, const float *in_dev, int64_t rows, in
                          int64_t in_col_stride, float *out_dev, int64_t out_row_stride, int64_t out_col_stride,
                          void *stream);
 
+/* ---- allocation-free variant (no counterpart in the reference) ----
+ * power_stats_static : the level metrics of b200vec_power_stats for callers that may not allocate (code under
+ *                      CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  It takes no
+ *                      context and calls no cudaMalloc / cudaFree / allocating routine: the scratch of its two-stage
+ *                      reduction is a file-scope `static __device__` array of 256 KiB + 256 B that every GPU
+ *                      loading the library holds until exit (one partial per 65 536 samples, 16 384 partials).
+ *                      LIMIT: n <= 2^30 samples per call; larger n is refused with an error, nothing is launched.
+ *                      stats_out_dev (DEVICE, 2 doubles, caller-owned): [0] = max |y|^2, [1] = sum of
+ *                      fl32(fl32(|y|)^2) in fp64, y = fl(x * pre_scale); the sum is taken in a fixed order, so
+ *                      it is reproducible run to run and equals b200vec_power_stats' to fp64 rounding (~1e-15
+ *                      relative), the max bit for bit.  Queued on `stream`, does not synchronise.  The first call
+ *                      on a device resolves the array's device address (cudaGetSymbolAddress): make it before
+ *                      any capture.  All calls on one GPU share the array: calls that overlap on the GPU (two
+ *                      streams, two threads) race; serialise them. */
+int b200vec_power_stats_static(int device, const void *in_dev, int64_t n, float pre_scale, double *stats_out_dev,
+                               void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -93,6 +93,7 @@ _SIGNATURES = {
                                        C.c_void_p]),
     "b200vec_wv_quantize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]),
     "b200vec_power_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(C.c_double), C.c_void_p]),
+    "b200vec_power_stats_static": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]),
     "b200vec_box_energy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200vec_threshold_bounds": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.POINTER(C.c_int64), C.c_void_p]),
     "b200vec_median2_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,

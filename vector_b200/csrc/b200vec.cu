@@ -1,5 +1,6 @@
 // b200vec.cu — C-ABI of libb200vec.so (see include/b200vec.h for the contract and the
 // reference lines each entry point replaces).  sm_100a only; no CPU fallback.
+#include <mutex>
 #include "common.cuh"
 #include "bank.cuh"
 #include "place.cuh"
@@ -127,6 +128,107 @@ static int run_select(b200vec_ctx *ctx, const float *data, long long n, int flag
                             cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaStreamSynchronize(st));
     memcpy(host_state, ctx->pinned, sizeof(SelState));
+    return 0;
+}
+
+// ---- b200vec_power_stats_static: the level metrics with NO allocation anywhere on the call path ----------
+// The scratch of the two-stage reduction lives in a file-scope device array that every GPU loading the library
+// holds until exit: one (max, sum) partial per chunk of kStaticChunk samples + the ticket that elects the
+// last block.  kStaticMaxPartials chunks bound the input: 2^30 samples (8 GiB of complex64) for 256 KiB + 256 B.
+constexpr int kStaticChunk = 1 << 16;                 // samples per partial
+constexpr int kStaticMaxPartials = 1 << 14;
+constexpr long long kStaticMaxSamples = (long long)kStaticChunk * kStaticMaxPartials;
+constexpr int kStaticMaxDevices = 64;
+
+struct StaticScratch {
+    double2 part[kStaticMaxPartials];                 // .x = max |y|^2, .y = sum fl32(fl32(|y|)^2) of chunk c
+    unsigned int ticket;                              // blocks that have finished; must be 0 at launch
+    unsigned int pad[63];
+};
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+// Fixed-order block reduction (shuffles, then the 8 warp results in order): the result does not depend on
+// the grid size or on which block got which chunk.
+__device__ __forceinline__ void static_block_reduce(double &mx, double &sum, double *sh) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    }
+    const int w = threadIdx.x >> 5;
+    __syncthreads();                                  // sh may still be read from the previous round
+    if ((threadIdx.x & 31) == 0) { sh[2 * w] = mx; sh[2 * w + 1] = sum; }
+    __syncthreads();
+    mx = sh[0]; sum = sh[1];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) { mx = fmax(mx, sh[2 * i]); sum += sh[2 * i + 1]; }
+}
+
+__global__ void __launch_bounds__(256)
+power_stats_static_kernel(const float2 *__restrict__ in, long long n, int n_parts, float pre_scale,
+                          StaticScratch *__restrict__ sc, double *__restrict__ out) {
+    __shared__ double sh[16];
+    __shared__ bool last;
+    for (int c = blockIdx.x; c < n_parts; c += gridDim.x) {
+        const long long lo = (long long)c * kStaticChunk;
+        const long long hi = lo + kStaticChunk < n ? lo + kStaticChunk : n;
+        double mx = 0.0, sum = 0.0;
+        for (long long i = lo + threadIdx.x; i < hi; i += 256) {
+            const float2 v = __ldg(in + i);
+            const float x = __fmul_rn(v.x, pre_scale), y = __fmul_rn(v.y, pre_scale);
+            const double e = (double)x * (double)x + (double)y * (double)y;
+            const float a = (float)sqrt(e);
+            mx = fmax(mx, e);
+            sum += (double)__fmul_rn(a, a);
+        }
+        static_block_reduce(mx, sum, sh);
+        if (threadIdx.x == 0) sc->part[c] = make_double2(mx, sum);
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(&sc->ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    double mx = 0.0, sum = 0.0;
+    for (int c = threadIdx.x; c < n_parts; c += 256) {
+        const double2 p = __ldcg(&sc->part[c]);
+        mx = fmax(mx, p.x);
+        sum += p.y;
+    }
+    static_block_reduce(mx, sum, sh);
+    if (threadIdx.x == 0) {
+        out[0] = mx; out[1] = sum;
+        sc->ticket = 0;                               // left clean for the next call
+    }
+}
+
+struct StaticDevice {
+    StaticScratch *scratch = nullptr;                 // cudaGetSymbolAddress of g_static_scratch ON this device
+    int sm_count = 0;
+    bool ready = false;
+};
+static StaticDevice g_static_dev[kStaticMaxDevices];
+static std::mutex g_static_mutex;
+
+// Once per device, with that device current: in host code `g_static_scratch` is only a handle for the runtime,
+// the address a kernel can use comes from cudaGetSymbolAddress.
+static int static_device_setup(int device, StaticDevice **out) {
+    std::lock_guard<std::mutex> lk(g_static_mutex);
+    StaticDevice &d = g_static_dev[device];
+    if (!d.ready) {
+        int major = 0;
+        B2_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+        if (major != 10)
+            return fail("b200vec_power_stats_static", "kernels are built for sm_100a only (need a Blackwell B200-class GPU)");
+        B2_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, device));
+        void *p = nullptr;
+        B2_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) return fail("b200vec_power_stats_static", "cudaGetSymbolAddress returned a NULL scratch address");
+        d.scratch = reinterpret_cast<StaticScratch *>(p);
+        d.ready = true;
+    }
+    *out = &d;
     return 0;
 }
 
@@ -1290,6 +1392,39 @@ int b200vec_median2_rows(b200vec_ctx *ctx, const float *in_dev, int64_t rows, in
     const int cols_fast = llabs(in_col_stride) <= llabs(in_row_stride);   // walk the contiguous direction with threadIdx
     median2_rows_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(in_dev, rows, cols, in_row_stride, in_col_stride,
                                                                           out_dev, out_row_stride, out_col_stride, cols_fast);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// The level metrics of b200vec_power_stats without a context and without any allocation: the scratch is the
+// file-scope device array above (set-up per device on the first call: cudaGetSymbolAddress with that device
+// current), the result goes to the caller's device buffer and nothing synchronises.  No counterpart in the
+// reference.
+int b200vec_power_stats_static(int device, const void *in_dev, int64_t n, float pre_scale, double *stats_out_dev,
+                               void *stream) {
+    B2_REQUIRE(stats_out_dev && n >= 0 && (n == 0 || in_dev), "NULL argument");
+    B2_REQUIRE(device >= 0 && device < kStaticMaxDevices, "device ordinal out of range (0..63)");
+    if (n > kStaticMaxSamples)
+        return fail("b200vec_power_stats_static",
+                    "n exceeds the static scratch: at most 2^30 (1073741824) samples per call; use b200vec_power_stats");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0)
+        return fail("b200vec_power_stats_static", "no CUDA device available (this library has no CPU fallback)");
+    B2_REQUIRE(device < count, "device ordinal out of range");
+    DeviceGuard g(device);
+    StaticDevice *d = nullptr;
+    if (int rc = static_device_setup(device, &d)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        B2_CUDA(cudaMemsetAsync(stats_out_dev, 0, 2 * sizeof(double), st));
+        return 0;
+    }
+    B2_CUDA(cudaMemsetAsync(&d->scratch->ticket, 0, sizeof(unsigned int), st));     // the array keeps the last call's contents
+    const int n_parts = (int)((n + kStaticChunk - 1) / kStaticChunk);
+    const int cap = d->sm_count * 8;
+    const int grid = n_parts < cap ? n_parts : cap;
+    power_stats_static_kernel<<<(unsigned)grid, 256, 0, st>>>((const float2 *)in_dev, n, n_parts, pre_scale,
+                                                               d->scratch, stats_out_dev);
     B2_CUDA(cudaGetLastError());
     return 0;
 }
