@@ -157,6 +157,15 @@ int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_
                  int64_t frame_lo, int64_t n_frames, float *out_dev, int64_t out_ld,
                  int *nonzero_flag_dev, void *stream);
 
+/* The same call for a double-precision signal: scipy.signal.spectrogram on complex128 input (create_spectrogram
+ * given np.complex128 / np.float64 data, utils.py:281-291) multiplies by the float64 window, transforms with the
+ * complex128 FFT and returns a float64 PSD.  in_dev: complex128 (16-byte aligned), window_dev: nperseg float64 taps,
+ * out_dev: float64 [nfft, out_ld].  nfft must be a power of two in [32, 8192] (16 B of shared memory per bin). */
+int b200vec_stft_f64(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_t in_len,
+                     int64_t stride, int nperseg, int hop, int nfft, const double *window_dev, double scale,
+                     int64_t frame_lo, int64_t n_frames, double *out_dev, int64_t out_ld,
+                     int *nonzero_flag_dev, void *stream);
+
 /* ---- fused build + full-rate spectrogram (the BASELINE cfg2 + cfg3 step in ONE kernel) -----
  * Pass B of b200vec_build (mode STORE or SCALE) and b200vec_stft for the fixed analysis shape of
  * vector_analyzer/spectrogram_analysis.py:35-49 (nperseg = nfft = 1024, hop = 512, stride 1,

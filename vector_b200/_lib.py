@@ -61,6 +61,9 @@ _SIGNATURES = {
     "b200vec_stft": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int,
                                C.c_int, C.c_int, C.c_void_p, C.c_float, C.c_int64, C.c_int64,
                                C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "b200vec_stft_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int,
+                                   C.c_int, C.c_int, C.c_void_p, C.c_double, C.c_int64, C.c_int64,
+                                   C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "b200vec_build_stft1024": (C.c_int, [C.c_void_p, C.POINTER(PktDesc), C.c_int, C.c_int64, C.c_int64,
                                          C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_float,
                                          C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),

@@ -363,15 +363,23 @@ compute_freq_ranges = H.compute_freq_ranges
 def _run_plan(eng, x_dev, plan, flag, stride):
     plan = H.resolve_plan(plan)                      # may raise ValueError like scipy would
     flag.zero_()
+    if x_dev.dtype == torch.complex128 and plan.nfft <= 8192:        # scipy's float64 path, in float64
+        S = eng.stft_f64(x_dev, plan.window, plan.nperseg, plan.noverlap, plan.nfft, plan.fs,
+                         scaling=plan.scaling, stride=stride, flag=flag)
+        return plan, S
+    dbl = x_dev.dtype == torch.complex128                            # nfft 16384 does not fit in float64: float32, widened
+    if dbl:
+        x_dev, stride = x_dev[::stride].to(torch.complex64), 1
     S = eng.stft(x_dev, plan.window, plan.nperseg, plan.noverlap, plan.nfft, plan.fs,
                  scaling=plan.scaling, stride=stride, flag=flag)
-    return plan, S
+    return plan, (S.to(torch.float64) if dbl else S)
 
 
 def create_spectrogram_device(sig_dev, sr, center_freq=0, max_samples=2_000_000,
                               time_resolution_us=1, adaptive_resolution=True, engine=None):
     """create_spectrogram on a complex64 CUDA tensor; returns (freqs f64, times f64, Sxx CUDA
-    float32 [nfft, frames]).  Follows utils.py:161-353 including the fallback chain.  A decimated
+    float32 [nfft, frames]).  A complex128 tensor takes scipy's double-precision path (float64 window, FFT
+    and PSD: b200vec_stft_f64) and returns a float64 Sxx.  Follows utils.py:161-353 including the fallback chain.  A decimated
     preview (heavy signals, utils.py:192-195) gathers sig[::factor] ONCE into a compact buffer
     (b200vec_decimate) that the overlapping frames then read — the same samples and arithmetic as
     transforming the strided view."""
@@ -384,8 +392,8 @@ def create_spectrogram_device(sig_dev, sr, center_freq=0, max_samples=2_000_000,
         print(f"🔍 Heavy packet detected: {n:,} samples ({n/sr:.2f}s)")
         print(f"📉 Downsampled by factor {plan0.factor}: {plan0.n_dec:,} samples")
     x, stride = sig_dev, plan0.factor
-    if stride > 1 and plan0.nperseg >= 2 * plan0.hop:            # frames overlap: read the strided samples once
-        x, stride = eng.decimate(sig_dev, stride), 1
+    if stride > 1 and plan0.nperseg >= 2 * plan0.hop and sig_dev.dtype == torch.complex64:
+        x, stride = eng.decimate(sig_dev, stride), 1             # frames overlap: read the strided samples once
     flag = eng._flag
     fb = H.fallback_plans(plan0)
     try:
@@ -405,20 +413,18 @@ def create_spectrogram_device(sig_dev, sr, center_freq=0, max_samples=2_000_000,
 def create_spectrogram(sig, sr, center_freq=0, max_samples=2_000_000, time_resolution_us=1,
                        adaptive_resolution=True):
     """Drop-in for utils.create_spectrogram (utils.py:161-353): numpy in, (freqs, times, Sxx)
-    numpy out, Sxx C-contiguous [nfft, frames] with fftshifted rows.  The arithmetic is
-    float32 (the reference's own precision for complex64 input); double-precision input is
-    accepted, computed in float32 and returned as float64 to keep the dtype contract."""
+    numpy out, Sxx C-contiguous [nfft, frames] with fftshifted rows.  The arithmetic is that of
+    scipy for the input's precision: float32 for complex64 / float32 data (the reference's own case),
+    float64 for complex128 / float64 data (b200vec_stft_f64), with a float64 Sxx as scipy returns."""
     if len(sig) == 0:
         raise ValueError("Signal is empty")
     a = np.asarray(sig)
     eng = get_engine()
-    dev = torch.from_numpy(np.ascontiguousarray(a.astype(np.complex64, copy=False))).to(eng.device)
+    wide = np.result_type(a.dtype, np.complex64) == np.complex128           # scipy's outdtype rule
+    dev = torch.from_numpy(np.ascontiguousarray(a.astype(np.complex128 if wide else np.complex64, copy=False))).to(eng.device)
     f, t, S = create_spectrogram_device(dev, sr, center_freq, max_samples, time_resolution_us,
                                         adaptive_resolution, engine=eng)
-    out = S.cpu().numpy()
-    if a.dtype in (np.complex128, np.float64):
-        out = out.astype(np.float64)
-    return f, t, out
+    return f, t, S.cpu().numpy()
 
 
 def full_rate_spectrogram_device(sig_dev, fs, center_freq=0.0, engine=None, **kw):

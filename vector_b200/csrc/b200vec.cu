@@ -269,6 +269,8 @@ int b200vec_create(int device, b200vec_ctx **out) {
                                  B200VEC_MAX_RANKS * kBins2 * 4));
     B2_CUDA(cudaFuncSetAttribute(stft_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  200 * 1024));
+    B2_CUDA(cudaFuncSetAttribute(stft_generic_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 200 * 1024));
     if (stft1024_setup() || fused1024_setup() || wf1024_setup() || span_setup()) { delete ctx; return 1; }
 #ifdef B2_AB
     if (pipe1024_setup()) { delete ctx; return 1; }
@@ -748,6 +750,40 @@ int b200vec_stft(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_
     const long long grid = (n_frames + a.T - 1) / a.T;
     B2_REQUIRE(grid < (1LL << 31), "too many frames for one launch");
     stft_generic_kernel<<<(unsigned)grid, kStftThreads, smem, st>>>(a);
+    B2_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// scipy's float64 path (complex128 input): window, FFT and PSD in double.
+int b200vec_stft_f64(b200vec_ctx *ctx, const void *in_dev, int64_t in_origin, int64_t in_len,
+                     int64_t stride, int nperseg, int hop, int nfft, const double *window_dev,
+                     double scale, int64_t frame_lo, int64_t n_frames, double *out_dev,
+                     int64_t out_ld, int *nonzero_flag_dev, void *stream) {
+    B2_REQUIRE(ctx && in_dev && out_dev && window_dev, "NULL argument");
+    B2_REQUIRE(nfft >= 32 && nfft <= 8192 && (nfft & (nfft - 1)) == 0,
+               "nfft must be a power of two in [32, 8192] for the float64 STFT");
+    B2_REQUIRE(nperseg >= 1 && nperseg <= nfft, "nfft must be greater than or equal to nperseg.");
+    B2_REQUIRE(hop >= 1, "noverlap must be less than nperseg.");
+    B2_REQUIRE(stride >= 1 && in_len >= 0 && n_frames >= 0 && out_ld >= n_frames, "bad geometry");
+    B2_REQUIRE(((uintptr_t)in_dev & 15) == 0, "in_dev must be 16-byte aligned");
+    if (n_frames == 0) return 0;
+    {
+        const long long first = frame_lo * (long long)hop * stride - in_origin;
+        const long long last = ((frame_lo + n_frames - 1) * (long long)hop + nperseg - 1) * stride - in_origin;
+        B2_REQUIRE(frame_lo >= 0 && first >= 0 && last < in_len, "frames read outside the input buffer");
+    }
+    DeviceGuard g(ctx->device);
+    Stft64Args a;
+    a.in = (const double2 *)in_dev; a.in_origin = in_origin; a.in_len = in_len; a.stride = stride;
+    a.nperseg = nperseg; a.hop = hop; a.nfft = nfft; a.log2n = ceil_log2(nfft);
+    a.window = window_dev; a.scale = scale; a.frame_lo = frame_lo; a.n_frames = n_frames;
+    a.out = out_dev; a.out_ld = out_ld; a.flag = nonzero_flag_dev;
+    a.T = stft64_pick_T(nfft);
+    if (get_twiddles64(ctx, nfft, &a.tw)) return 1;
+    const size_t smem = (size_t)nfft * 16 + (a.T > 1 ? (size_t)nfft * 8 * (a.T + 1) : 0);
+    const long long grid = (n_frames + a.T - 1) / a.T;
+    B2_REQUIRE(grid < (1LL << 31), "too many frames for one launch");
+    stft_generic_f64_kernel<<<(unsigned)grid, kStftThreads, smem, (cudaStream_t)stream>>>(a);
     B2_CUDA(cudaGetLastError());
     return 0;
 }

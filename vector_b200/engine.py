@@ -280,6 +280,29 @@ class Engine:
         self.launches += 1
         return out
 
+    def stft_f64(self, x, window, nperseg, noverlap, nfft, fs, scaling="density", stride=1, flag=None):
+        """|STFT|^2*scale of x[::stride] for a complex128 CUDA tensor -> float64 [nfft, n_frames], rows fftshifted:
+        scipy's double-precision path (b200vec_stft_f64), window taps and scale in float64."""
+        x = x.reshape(-1)
+        hop = nperseg - noverlap
+        n_dec = (x.numel() + stride - 1) // stride
+        n_frames = 0 if n_dec < nperseg else (n_dec - nperseg) // hop + 1
+        key = (window, nperseg, float(fs), scaling, "f64")
+        if key not in self._windows:
+            taps, scale = H.window_and_scale(window, nperseg, fs, scaling, dtype=np.complex128)
+            self._windows[key] = (torch.from_numpy(np.ascontiguousarray(taps, dtype=np.float64)).to(self.device),
+                                  float(scale))
+        taps, scale = self._windows[key]
+        pitch = max((n_frames + 15) // 16 * 16, 16)
+        out = torch.empty((nfft, pitch), dtype=torch.float64, device=self.device)[:, :n_frames]
+        if n_frames > 0:
+            check(self.lib.b200vec_stft_f64(self._ctx, self._ptr(x), 0, x.numel(), int(stride), int(nperseg), int(hop),
+                                            int(nfft), self._ptr(taps), scale, 0, int(n_frames), self._ptr(out),
+                                            out.stride(0), self._ptr(flag) if flag is not None else None,
+                                            self._stream()))
+            self.launches += 1
+        return out
+
     def replicate_frames(self, spec, frame_src0, period_frames, frame_dst0, n_frames):
         """spec[:, frame_dst0 + i] = spec[:, frame_src0 + (frame_dst0 + i - frame_src0) % period_frames] for a
         frame-major spectrogram tensor (b200vec_replicate_frames): the periodic tiling of a dense vector's map."""

@@ -91,7 +91,8 @@ def window_and_scale(name, nperseg, fs, scaling, dtype=np.complex64):
         scale = 1.0 / win.sum() ** 2
     else:
         raise ValueError(f"Unknown scaling: {scaling!r}")
-    return np.ascontiguousarray(win.real), np.asarray(scale).real.astype(np.float32)[()]
+    real = np.float32 if np.dtype(dtype) == np.complex64 else np.float64     # complex128 input: everything in double
+    return np.ascontiguousarray(win.real), np.asarray(scale).real.astype(real)[()]
 
 
 # --------------------------------------------------------------------------- STFT plan
