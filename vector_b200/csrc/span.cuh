@@ -145,6 +145,11 @@ span_kernel(const __grid_constant__ SpanArgs a) {
     const unsigned long long keep = wf_policy_evict_last();
     const unsigned long long pol = wf_policy_evict_first();
     const long long gw = (long long)blockIdx.x * kSpWarps + warp, nw = (long long)gridDim.x * kSpWarps;
+    // The first work item of pass B is claimed here, ahead of the max pass: thousands of warps leaving the grid
+    // barrier together would otherwise queue up at the one counter (an atomic per clock at its L2 slice) before
+    // any of them stores a sample.
+    unsigned next = 0;
+    if (lane == 0 && a.mode != B200VEC_BUILD_MAXONLY) next = atomicAdd(a.ctr, 1u);
 
     if (a.mode == B200VEC_BUILD_MAXONLY || a.mode == kSpNorm) {
         // ---------------------------------------------------------------- pass A: max |v|^2 per vector, no stores
@@ -217,10 +222,8 @@ span_kernel(const __grid_constant__ SpanArgs a) {
     const long long ipv = (halves + kChunk - 1) / kChunk;                     // items per vector
     const long long n_items = ipv * a.n_vec;
     const bool scaled = a.mode == B200VEC_BUILD_SCALE || a.mode == kSpNorm;
-    unsigned next = 0;
     float scl = 1.0f;
     int scl_v = -1;
-    if (lane == 0) next = atomicAdd(a.ctr, 1u);
     for (;;) {
         const long long c = __shfl_sync(0xffffffffu, next, 0);
         if (c >= n_items) break;

@@ -274,6 +274,10 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         const double m2 = __longlong_as_double((long long)*a.maxsq);
         if (m2 > 0.0) scl = 1.0f / (float)sqrt(m2);        // numpy's complex64 / float32: multiply by the fp32 reciprocal
     }
+    // The first work item is claimed ahead of the max pass: the warps leave the grid barrier together and would
+    // otherwise queue up at the one counter before any of them places a sample.
+    unsigned next = 0;
+    if (lane == 0) next = atomicAdd(a.ctr, 1u);
     __syncthreads();
     if (norm_pass) {
         // Pass A inside the kernel: every warp evaluates its share of the spans that can hold the max of the
@@ -418,8 +422,6 @@ wf1024_kernel(const __grid_constant__ WfArgs a) {
         for (int j = 0; j < 16; ++j) x[j] = vst[lane + 32 * j];
     };
 
-    unsigned next = 0;
-    if (lane == 0) next = atomicAdd(a.ctr, 1u);
     for (;;) {
         const long long c = __shfl_sync(0xffffffffu, next, 0);
         if (c >= a.n_chunks) break;
